@@ -1,0 +1,154 @@
+"""Hand-derived Bookmark-Coloring cases pinning the oracle's restatement of
+J/bca/jobs/DirectedWeighted.java:31-101, UndirectedWeighted.java:31-114, J/bca/util/BCV.java.
+Expected values are written out from the rules (fp64 paint, f32 accumulate in pop order)."""
+import numpy as np
+
+import oracle
+from graph_embeddings_b200 import synth
+
+f32 = np.float32
+A, E = 0.1, 1e-3
+
+
+def coo(c):
+    i, j, x = c.sorted()
+    return {(int(a), int(b)): f32(v) for a, b, v in zip(i, j, x)}
+
+
+def test_isolated_node_directed():
+    c = oracle.cooc_build(synth.tiny([], V=1), A, E, True)
+    # forward pop: 0f + (float)(0.1*1.0); reverse the same; merge = Float::sum
+    assert coo(c) == {(0, 0): f32(0.1) + f32(0.1)}
+    assert c.nnz == 1 and c.pops == 2 and c.scanned == 0
+    assert c.max == float(f32(0.1) + f32(0.1))
+
+
+def test_single_edge_directed():
+    c = coo(oracle.cooc_build(synth.tiny([(0, 1, 1.0)]), A, E, True))
+    p1 = (1 - A) * 1.0 * (1.0 / 1.0)          # paint arriving at the neighbour
+    assert c == {
+        (0, 0): f32(0.1) + f32(0.1),         # fwd root + rev root
+        (0, 1): f32(A * p1),                  # fwd only
+        (1, 1): f32(0.1) + f32(0.1),
+        (1, 0): f32(A * p1),                  # rev only (follows the in-edge)
+    }
+
+
+def _geometric(alpha, eps):
+    """2-cycle / self-loop: the paint bounces with factor (1-alpha); returns the f32 sums at
+    the root (even pops) and at the other node (odd pops)."""
+    paint, k = 1.0, 0
+    acc = [None, None]
+    while True:
+        v = f32(alpha * paint)
+        acc[k & 1] = v if acc[k & 1] is None else f32(acc[k & 1] + v)
+        if paint < eps:
+            break
+        nxt = (1 - alpha) * paint * (1.0 / 1.0)
+        if nxt < eps:
+            break
+        paint, k = nxt, k + 1
+    return acc, k + 1
+
+
+def test_two_cycle_directed():
+    c = oracle.cooc_build(synth.tiny([(0, 1, 1.0), (1, 0, 1.0)]), A, E, True)
+    (root, other), pops = _geometric(A, E)
+    assert pops == 66                         # 0.9^65 >= 1e-3 > 0.9^66
+    got = coo(c)
+    # forward and reverse passes are identical on a symmetric 2-cycle
+    assert got == {(0, 0): f32(root + root), (0, 1): f32(other + other),
+                   (1, 1): f32(root + root), (1, 0): f32(other + other)}
+    assert c.pops == 4 * pops
+
+
+def test_self_loop_directed():
+    c = coo(oracle.cooc_build(synth.tiny([(0, 0, 1.0)]), A, E, True))
+    # every pop is node 0: one f32 running sum over all 66 pops, forward == reverse
+    paint, s = 1.0, None
+    for _ in range(66):
+        v = f32(A * paint)
+        s = v if s is None else f32(s + v)
+        paint = (1 - A) * paint * (1.0 / 1.0)
+    assert c == {(0, 0): f32(s + s)}
+
+
+def test_weighted_star_and_epsilon_cut():
+    g = synth.tiny([(0, 1, 1.0), (0, 2, 0.1)])
+    total = 1.0 + float(f32(0.1))             # fp64 sum of the f32 weights
+    p1 = (1 - A) * 1.0 * (1.0 / total)
+    p2 = (1 - A) * 1.0 * (float(f32(0.1)) / total)
+    c = coo(oracle.cooc_build(g, A, E, True))
+    assert c[(0, 1)] == f32(A * p1) and c[(0, 2)] == f32(A * p2)
+    assert c[(1, 0)] == f32(A * 0.9) and c[(2, 0)] == f32(A * 0.9)   # reverse: single in-edge
+    # with epsilon = 0.1 the light edge's share (0.0818) is dropped before insertion
+    c = coo(oracle.cooc_build(g, A, 0.1, True))
+    assert (0, 2) not in c and c[(0, 1)] == f32(A * p1)
+    # epsilon > 1: the root itself does not distribute
+    c = coo(oracle.cooc_build(g, A, 2.0, True))
+    assert set(c) == {(0, 0), (1, 1), (2, 2)}
+
+
+def test_undirected_follows_both_directions():
+    # single edge 0->1, undirected: bookmark 1 reaches 0 through the in-edge, then bounces
+    c = oracle.cooc_build(synth.tiny([(0, 1, 1.0)]), A, E, False)
+    (root, other), pops = _geometric(A, E)
+    assert coo(c) == {(0, 0): root, (0, 1): other, (1, 1): root, (1, 0): other}
+    assert c.pops == 2 * pops
+
+
+def test_undirected_node_in_both_lists_gets_out_then_in():
+    # 0->1 (w 1) and 1->0 (w .5), undirected, eps=.25: from 0, node 1 is out- and
+    # in-neighbour, so it receives two adds in the order out, in (UndirectedWeighted.java:73-111)
+    g = synth.tiny([(0, 1, 1.0), (1, 0, 0.5)])
+    eps = 0.25
+    c = coo(oracle.cooc_build(g, A, eps, False))
+    t0 = 1.0 + 0.5                                   # node 0: out {1: 1.0} then in {1: 0.5}
+    t1 = 0.5 + 1.0                                   # node 1: out {0: 0.5} then in {0: 1.0}
+    k = 1 - A
+    n1 = k * 1.0 * (1.0 / t0) + k * 1.0 * (0.5 / t0)          # .6 then +.3, both >= eps
+    n0 = k * n1 * (0.5 / t1) + k * n1 * (1.0 / t1)            # .27 then +.54
+    n1b = k * n0 * (1.0 / t0)                                  # .486 ; in-share .243 < eps dropped
+    assert k * n0 * (0.5 / t0) < eps <= n1b
+    n0b = k * n1b * (1.0 / t1)                                 # .2916 ; out-share .1458 dropped
+    assert k * n1b * (0.5 / t1) < eps <= n0b
+    assert k * n0b * (1.0 / t0) < eps                          # nothing left to distribute
+    assert c[(0, 0)] == f32(f32(f32(A * 1.0) + f32(A * n0)) + f32(A * n0b))
+    assert c[(0, 1)] == f32(f32(A * n1) + f32(A * n1b))
+
+
+def test_normalise_counts_and_unity():
+    g = synth.tiny([(0, 1, 1.0), (0, 2, 0.1)])
+    raw = oracle.cooc_build(g, A, E, True)
+    r = coo(raw)
+    row0 = [r[(0, 0)], r[(0, 1)], r[(0, 2)]]
+    mx, mn = max(row0), min(row0)
+    cnt = coo(oracle.cooc_build(g, A, E, True, "counts"))
+    assert (0, 0) not in cnt                                  # root removed (BCV.java:58)
+    for j in (1, 2):
+        assert cnt[(0, j)] == f32(f32(r[(0, j)] / f32(f32(mx - mn) / f32(999.0))) + f32(1.0))
+    un = oracle.cooc_build(g, A, E, True, "unity")
+    u = coo(un)
+    s = f32(r[(0, 1)] + r[(0, 2)])                            # discovery order: 1 then 2
+    assert u[(0, 1)] == f32(f32(r[(0, 1)] / s) - f32(1e-6))
+    assert u[(0, 2)] == f32(f32(r[(0, 2)] / s) - f32(1e-6))
+    assert (0, 0) not in u
+    # rows 1 and 2 keep one entry (the reverse hit on node 0)
+    assert u[(1, 0)] == f32(f32(1.0) - f32(1e-6))
+
+
+def test_empty_row_after_root_removal_sets_max_to_one():
+    c = oracle.cooc_build(synth.tiny([], V=2), A, E, True, "unity")
+    assert c.nnz == 0 and c.max == 1.0                        # BCV.max() of empty -> 1f
+
+
+def test_thread_count_does_not_change_result():
+    g = synth.rmat(3000, 20000, 9)
+    a = oracle.cooc_build(g, threads=1)
+    b = oracle.cooc_build(g, threads=4)
+    assert np.array_equal(a.I, b.I) and np.array_equal(a.J, b.J) and np.array_equal(a.X, b.X)
+    assert a.max == b.max and a.pops == b.pops
+    # sample window == corresponding rows of the full build
+    s = oracle.cooc_build(g, first=100, count=50)
+    lo, hi = a.row_off[100], a.row_off[150]
+    assert np.array_equal(s.J, a.J[lo:hi]) and np.array_equal(s.X, a.X[lo:hi])
