@@ -1,0 +1,119 @@
+// common.cuh — shared declarations of libgraphemb.so (sm_100a only; no CPU fallback).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/graphemb.h"
+
+#define GE_CUDA(call)                                                                        \
+    do {                                                                                     \
+        cudaError_t e__ = (call);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e__);                  \
+            return e__ == cudaErrorMemoryAllocation ? GE_ERR_NOMEM : GE_ERR_CUDA;            \
+        }                                                                                    \
+    } while (0)
+
+// ---- java.util.Random as an affine map over Z/2^48 (JDK Javadoc; the reference draws through
+// J/util/rnd/ExtendedRandom.java:27-35).  Usable on host and device. ---------------------------
+struct JavaLcg {
+    static constexpr uint64_t MULT = 0x5DEECE66DULL, ADD = 0xBULL, MASK = (1ULL << 48) - 1;
+    uint64_t s;
+    __host__ __device__ static JavaLcg seeded(int64_t seed) { return JavaLcg{((uint64_t)seed ^ MULT) & MASK}; }
+    __host__ __device__ inline int32_t next(int bits) {
+        s = (s * MULT + ADD) & MASK;
+        return (int32_t)(int64_t)(s >> (48 - bits));
+    }
+    // O(log n) skip of n draws: compose the affine map with itself by squaring.
+    __host__ __device__ inline void jump(uint64_t n) {
+        uint64_t a = MULT, c = ADD, A = 1, C = 0;
+        while (n) {
+            if (n & 1) { A = (A * a) & MASK; C = (C * a + c) & MASK; }
+            c = ((a + 1) * c) & MASK;
+            a = (a * a) & MASK;
+            n >>= 1;
+        }
+        s = (A * s + C) & MASK;
+    }
+    __host__ __device__ inline float nextFloat() { return (float)next(24) / (float)(1 << 24); }
+    // Random.nextInt(bound), JDK 8 (power-of-two fast path + rejection loop)
+    __host__ inline int32_t nextInt(int32_t bound) {
+        int32_t r = next(31);
+        const int32_t m = bound - 1;
+        if ((bound & m) == 0) return (int32_t)(((int64_t)bound * (int64_t)r) >> 31);
+        for (int32_t u = r;; u = next(31)) {
+            r = u % bound;
+            if ((int32_t)((uint32_t)u - (uint32_t)r + (uint32_t)m) >= 0) return r;
+        }
+    }
+};
+
+// One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128):
+//   FAST math : a = (float)log(x) [glove] or (float)log(x/(1-x)) [pglove], b = f(x) weight
+//   JAVA math : a = x, b unused (log/pow are evaluated in fp64 inside the kernel)
+struct __align__(16) NzEntry {
+    int32_t i, j;
+    float a, b;
+};
+
+struct DistState;  // dist.cu
+
+struct ge_ctx {
+    ge_config cfg;
+    std::string err;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+
+    // --- graph (A1) ---
+    int32_t V = 0;
+    int64_t E_out = 0, E_in = 0;
+    int64_t *d_out_off = nullptr, *d_in_off = nullptr;
+    int32_t *d_out_nbr = nullptr, *d_in_nbr = nullptr;
+    float *d_out_w = nullptr, *d_in_w = nullptr;
+    double *d_out_total = nullptr, *d_in_total = nullptr;  // per-node fp64 weight sums
+    float *d_out_wmax = nullptr, *d_in_wmax = nullptr;      // per-node heaviest edge (pruning bound)
+
+    // --- co-occurrence matrix (A6) ---
+    int64_t nnz = 0;
+    double xmax = 0;
+    bool have_cooc = false;
+    int32_t *d_I = nullptr, *d_J = nullptr;
+    float* d_X = nullptr;
+    int64_t* d_row_off = nullptr;  // row_count+1 offsets when built here (rows contiguous), else null
+    int32_t row_first = 0, row_count = 0;
+    int64_t bca_overflow_rows = 0;  // rows that needed the global-memory table tier
+    int64_t bca_pops = 0, bca_scanned = 0;
+    double bca_seconds = 0;
+
+    // --- embedding store (B1): two arrays of V rows x S floats,
+    //     row = [vec(D4) | gradsq(D4) | bias | gradsq_bias | pad], S = roundup(2*D4+2, 8) ---
+    int32_t D4 = 0, S = 0;
+    float *d_W = nullptr, *d_C = nullptr;
+    bool have_store = false;
+    NzEntry* d_nz = nullptr;      // packed nonzeros
+    int32_t* d_perm = nullptr;    // GE_ORDER_JAVA only
+    std::vector<int32_t> h_perm;  // GE_ORDER_JAVA host replay
+    JavaLcg rng{0};               // stream position after init (GE_ORDER_JAVA)
+    double* d_cost = nullptr;     // epoch cost accumulator
+    int32_t epoch = 0;
+    std::vector<double> history;
+    double update_seconds = 0;
+    int64_t launches = 0, updates = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    DistState* dist = nullptr;
+};
+
+// train.cu
+int ge_train_prepare(ge_ctx* ctx);  // pack nonzeros, allocate cost/perm
+int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
+                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st);
+void ge_free_store(ge_ctx* ctx);
+// bca.cu
+int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);
+void ge_free_cooc(ge_ctx* ctx);
+// dist.cu
+void ge_dist_free(ge_ctx* ctx);

@@ -1,0 +1,548 @@
+// train.cu — embedding store + GloVe / pGloVe AdaGrad update (K4, K5, K6, K8 of SURVEY §2.3).
+//
+// Replaces J/opt/Optimizer.java (store :45-57, extractResult :130-140) and the per-nonzero
+// loop of J/opt/grad/Adagrad.java:49-95 with GloveCost.java:7-20 / PGloveCost.java:7-20.
+//
+// K6 is HBM-bound gather / FMA / scatter: one warp owns one nonzero at a time, the two
+// store rows (W_i|Gw_i|b_i|Gb_i and C_j|Gc_j|b_j|Gb_j) are each ONE contiguous block of S
+// floats read with 128-bit loads that bypass L1 (ld.global.cg: Hogwild readers must see other
+// SMs' writes) and written back with 128-bit stores.  Algorithmic bytes per nonzero:
+// 32*dim + 44.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace {
+
+__device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Keyed bijection on [0, n): 4-round unbalanced Feistel over ceil(log2 n) bits + cycle walking.
+// Stands in for the reference's Fisher-Yates epoch shuffle (Permutation.java:21-23) in
+// GE_ORDER_DEVICE mode: a fresh pseudo-random order per epoch with no permutation array.
+struct Bijection {
+    uint64_t n;
+    uint32_t abits, bbits;
+    uint64_t key;
+    __host__ __device__ static Bijection make(uint64_t n, uint64_t key) {
+        uint32_t bits = 1;
+        while ((1ULL << bits) < n) bits++;
+        if (bits < 2) bits = 2;
+        Bijection b;
+        b.n = n; b.abits = bits / 2; b.bbits = bits - bits / 2; b.key = key;
+        return b;
+    }
+    __host__ __device__ inline uint32_t f(uint32_t x, uint32_t round) const {
+        uint64_t h = (uint64_t)x * 0x9E3779B97F4A7C15ULL + key + round * 0xD1B54A32D192ED03ULL;
+        h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ULL; h ^= h >> 32;
+        return (uint32_t)h;
+    }
+    __host__ __device__ inline uint64_t operator()(uint64_t k) const {
+        const uint32_t ma = (1u << abits) - 1, mb = (uint32_t)((1ULL << bbits) - 1);
+        do {
+            uint32_t L = (uint32_t)(k >> bbits) & ma, R = (uint32_t)k & mb;
+            L ^= f(R, 0) & ma;
+            R ^= f(L, 1) & mb;
+            L ^= f(R, 2) & ma;
+            R ^= f(L, 3) & mb;
+            k = ((uint64_t)L << bbits) | R;
+        } while (k >= n);
+        return k;
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// K6 — the update kernel.  NT = float4 chunks per lane per vector (dim <= 128*NT).
+// JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
+// ------------------------------------------------------------------------------------------
+template <int NT, bool JAVA>
+__global__ void __launch_bounds__(256)
+glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
+                     float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
+                     int32_t D4, int32_t S, int32_t method, double xmax, float lr,
+                     double* __restrict__ cost_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int nchunk = D4 >> 2;  // float4 chunks per vector
+    const double lr_d = (double)lr;
+    double cost_d = 0.0;
+    float cost_f = 0.0f;  // JAVA: the reference's f32 running cost (Adagrad.java:46,60)
+
+    for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
+        // lane l fetches the nonzero at shuffled position base + l
+        NzEntry mine = {0, 0, 0.f, 0.f};
+        const int64_t pos = base + lane;
+        if (pos < count) {
+            const int64_t idx = perm ? (int64_t)perm[pos] : (int64_t)bij((uint64_t)pos);
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(nz + idx));
+            mine.i = raw.x; mine.j = raw.y; mine.a = __int_as_float(raw.z); mine.b = __int_as_float(raw.w);
+        }
+        const int nvalid = (int)min((int64_t)32, count - base);
+        for (int t = 0; t < nvalid; t++) {
+            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
+            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
+            const float ea = __shfl_sync(0xffffffffu, mine.a, t);
+            const float eb = __shfl_sync(0xffffffffu, mine.b, t);
+            float* wrow = W + (size_t)bi * S;
+            float* crow = C + (size_t)bj * S;
+
+            float4 w[NT], c[NT], gw[NT], gc[NT];
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                const int ch = lane + 32 * q;
+                if (ch < nchunk) {
+                    w[q] = ldcg4(wrow + 4 * ch);
+                    c[q] = ldcg4(crow + 4 * ch);
+                    gw[q] = ldcg4(wrow + D4 + 4 * ch);
+                    gc[q] = ldcg4(crow + D4 + 4 * ch);
+                } else {
+                    w[q] = c[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    gw[q] = gc[q] = make_float4(1.f, 1.f, 1.f, 1.f);
+                }
+            }
+            float2 bw = __ldcg(reinterpret_cast<const float2*>(wrow + 2 * D4));  // (bias, gradsq)
+            float2 bc = __ldcg(reinterpret_cast<const float2*>(crow + 2 * D4));
+
+            float dot = 0.f;
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                if (JAVA) {  // keep f32 multiply and add separate as the JVM does
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].x, c[q].x));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].y, c[q].y));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].z, c[q].z));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].w, c[q].w));
+                } else {
+                    dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
+                }
+            }
+            dot = warp_sum(dot);
+
+            float inner, wc;
+            if (JAVA) {
+                // GloveCost.java:13 / PGloveCost.java:13, weightedCost :19
+                const float x = ea;
+                double target;
+                if (method == GE_METHOD_GLOVE) target = log((double)x);
+                else target = log((double)__fdiv_rn(x, __fsub_rn(1.0f, x)));
+                inner = (float)__dadd_rn((double)dot, __dsub_rn((double)__fadd_rn(bw.x, bc.x), target));
+                if (method == GE_METHOD_GLOVE)
+                    wc = ((double)x > xmax) ? inner : __fmul_rn((float)pow(__ddiv_rn((double)x, xmax), 0.75), inner);
+                else
+                    wc = __fmul_rn(x, inner);
+                // Adagrad.java:60 — cost = (float)(cost + 0.5*wc*inner), product in fp64
+                cost_f = (float)__dadd_rn((double)cost_f, __dmul_rn(__dmul_rn(0.5, (double)wc), (double)inner));
+            } else {
+                inner = dot + (bw.x + bc.x) - ea;
+                wc = eb * inner;
+                cost_d += 0.5 * (double)wc * (double)inner;
+            }
+
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                const int ch = lane + 32 * q;
+                if (ch < nchunk) {
+                    float* wv = reinterpret_cast<float*>(&w[q]);
+                    float* cv = reinterpret_cast<float*>(&c[q]);
+                    float* gwv = reinterpret_cast<float*>(&gw[q]);
+                    float* gcv = reinterpret_cast<float*>(&gc[q]);
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        if (JAVA) {  // Adagrad.java:72-80
+                            const float g1 = __fmul_rn(wc, cv[e]);
+                            const float g2 = __fmul_rn(wc, wv[e]);
+                            wv[e] = (float)__dsub_rn((double)wv[e], __dmul_rn(__ddiv_rn((double)g1, __dsqrt_rn((double)gwv[e])), lr_d));
+                            cv[e] = (float)__dsub_rn((double)cv[e], __dmul_rn(__ddiv_rn((double)g2, __dsqrt_rn((double)gcv[e])), lr_d));
+                            gwv[e] = __fadd_rn(gwv[e], __fmul_rn(g1, g1));
+                            gcv[e] = __fadd_rn(gcv[e], __fmul_rn(g2, g2));
+                        } else {
+                            const float g1 = wc * cv[e];
+                            const float g2 = wc * wv[e];
+                            wv[e] -= g1 * rsqrtf(gwv[e]) * lr;
+                            cv[e] -= g2 * rsqrtf(gcv[e]) * lr;
+                            gwv[e] += g1 * g1;
+                            gcv[e] += g2 * g2;
+                        }
+                    }
+                    st4(wrow + 4 * ch, w[q]);
+                    st4(crow + 4 * ch, c[q]);
+                    st4(wrow + D4 + 4 * ch, gw[q]);
+                    st4(crow + D4 + 4 * ch, gc[q]);
+                }
+            }
+            if (lane == 0) {  // Adagrad.java:88-93 — bias step has no learning rate
+                if (JAVA) {
+                    bw.x = (float)__dsub_rn((double)bw.x, __ddiv_rn((double)wc, __dsqrt_rn((double)bw.y)));
+                    bc.x = (float)__dsub_rn((double)bc.x, __ddiv_rn((double)wc, __dsqrt_rn((double)bc.y)));
+                    const float w2 = __fmul_rn(wc, wc);
+                    bw.y = __fadd_rn(bw.y, w2);
+                    bc.y = __fadd_rn(bc.y, w2);
+                } else {
+                    bw.x -= wc * rsqrtf(bw.y);
+                    bc.x -= wc * rsqrtf(bc.y);
+                    bw.y += wc * wc;
+                    bc.y += wc * wc;
+                }
+                *reinterpret_cast<float2*>(wrow + 2 * D4) = bw;
+                *reinterpret_cast<float2*>(crow + 2 * D4) = bc;
+            }
+            if (JAVA) __syncwarp();  // serial order: lane 0's bias store precedes the next loads
+        }
+    }
+    if (lane == 0) {
+        const double cst = JAVA ? (double)cost_f : cost_d;
+        if (cst != 0.0) atomicAdd(cost_out, cst);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// pack: (I, J, X) -> NzEntry.  FAST math folds log / pow (per-nonzero constants) into the
+// entry once, in fp64, so the hot loop has no transcendental (GloveCost.java:13,19).
+// ------------------------------------------------------------------------------------------
+__global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
+                              const float* __restrict__ X, int64_t nnz, int32_t method, int32_t java,
+                              double xmax, NzEntry* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const float x = X[k];
+        NzEntry e;
+        e.i = I[k]; e.j = J[k];
+        if (java) { e.a = x; e.b = 0.f; }
+        else if (method == GE_METHOD_GLOVE) {
+            e.a = (float)log((double)x);
+            e.b = ((double)x > xmax) ? 1.0f : (float)pow((double)x / xmax, 0.75);
+        } else {
+            e.a = (float)log((double)(x / (1.0f - x)));
+            e.b = x;
+        }
+        out[k] = e;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4 — store init.  One thread per row replays the row's (2 + 2*dim) draws; GE_INIT_JAVA jumps
+// the LCG to the row's stream position, so the result equals Optimizer.java:50-57 bit for bit.
+// value = (float)((double)nextFloat - 0.5) / (float)dim ; gradsq = 1 (Adagrad.java:27-33)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t counter24(uint64_t seed, uint64_t idx) {
+    uint64_t h = idx * 0x9E3779B97F4A7C15ULL + seed;
+    h ^= h >> 30; h *= 0xBF58476D1CE4E5B9ULL; h ^= h >> 27; h *= 0x94D049BB133111EBULL; h ^= h >> 31;
+    return (uint32_t)(h >> 40);
+}
+
+__global__ void store_init(float* __restrict__ W, float* __restrict__ C, int32_t V, int32_t dim,
+                           int32_t D4, int32_t S, int64_t seed, int32_t java, int32_t row0) {
+    const int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= V) return;
+    const uint64_t per_row = 2 + 2 * (uint64_t)dim;
+    const uint64_t first = (uint64_t)(row0 + r) * per_row;  // global draw index of this row
+    JavaLcg g = JavaLcg::seeded(seed);
+    if (java) g.jump(first);
+    uint64_t n = first;
+    const float fd = (float)dim;
+    auto draw = [&]() -> float {
+        const float u = java ? g.nextFloat() : (float)counter24((uint64_t)seed, n) / (float)(1 << 24);
+        n++;
+        return __fdiv_rn((float)((double)u - 0.5), fd);
+    };
+    float* w = W + (size_t)r * S;
+    float* c = C + (size_t)r * S;
+    w[2 * D4] = draw(); w[2 * D4 + 1] = 1.0f;
+    c[2 * D4] = draw(); c[2 * D4 + 1] = 1.0f;
+    for (int d = 0; d < dim; d++) {
+        w[d] = draw();
+        c[d] = draw();
+        w[D4 + d] = 1.0f;
+        c[D4 + d] = 1.0f;
+    }
+    for (int d = dim; d < D4; d++) { w[d] = c[d] = 0.f; w[D4 + d] = c[D4 + d] = 1.0f; }
+    for (int d = 2 * D4 + 2; d < S; d++) { w[d] = 0.f; c[d] = 0.f; }
+}
+
+// K8 — extractResult (Optimizer.java:130-140): (focus + context) / 2 in f32, widened
+template <typename T>
+__global__ void extract_avg(const float* __restrict__ W, const float* __restrict__ C, int32_t V,
+                            int32_t dim, int32_t S, T* __restrict__ out) {
+    const int64_t total = (int64_t)V * dim, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
+        const int64_t r = k / dim;
+        const int32_t d = (int32_t)(k - r * dim);
+        out[k] = (T)__fdiv_rn(__fadd_rn(W[r * S + d], C[r * S + d]), 2.0f);
+    }
+}
+
+// de-interleave one component of the store into the reference's array layout (validation)
+__global__ void store_component(const float* __restrict__ A, int32_t V, int32_t dim, int32_t S,
+                                int32_t off, int32_t width, float* __restrict__ out) {
+    const int64_t total = (int64_t)V * width, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
+        const int64_t r = k / width;
+        out[k] = A[r * S + off + (k - r * width)];
+    }
+}
+
+__global__ void materialise_order(Bijection bij, int64_t n, int32_t* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride)
+        out[k] = (int32_t)bij((uint64_t)k);
+}
+
+uint64_t epoch_key(int64_t seed, int32_t epoch) {
+    uint64_t h = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + (uint64_t)(epoch + 1) * 0xD6E8FEB86659FD93ULL;
+    h ^= h >> 32; h *= 0xD6E8FEB86659FD93ULL; h ^= h >> 32;
+    return h;
+}
+
+}  // namespace
+
+// ==========================================================================================
+// host side
+// ==========================================================================================
+template <bool JAVA>
+static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStream_t st,
+                            const NzEntry* nz, int64_t count, float* W, float* C,
+                            const int32_t* perm, Bijection bij, double* d_cost) {
+    const ge_config& c = ctx->cfg;
+#define GE_LAUNCH(NT_)                                                                            \
+    glove_adagrad_update<NT_, JAVA><<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4,  \
+                                                            ctx->S, c.method, ctx->xmax,         \
+                                                            c.learning_rate, d_cost)
+    switch (nt) {
+        case 1: GE_LAUNCH(1); break;
+        case 2: GE_LAUNCH(2); break;
+        case 3: GE_LAUNCH(3); break;
+        case 4: GE_LAUNCH(4); break;
+        case 6: GE_LAUNCH(6); break;
+        case 8: GE_LAUNCH(8); break;
+        default: ctx->err = "dim too large (max 1024)"; return GE_ERR_INVALID;
+    }
+#undef GE_LAUNCH
+    GE_CUDA(cudaGetLastError());
+    return GE_OK;
+}
+
+template <int NT, bool JAVA>
+static int blocks_per_sm() {
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, glove_adagrad_update<NT, JAVA>, 256, 0);
+    return n < 1 ? 1 : n;
+}
+
+int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
+                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st) {
+    if (count <= 0) return GE_OK;
+    int nt = (ctx->D4 / 4 + 31) / 32;
+    if (nt == 5) nt = 6;
+    if (nt == 7) nt = 8;
+    const bool java = ctx->cfg.math == GE_MATH_JAVA;
+    dim3 block(256), grid;
+    if (ctx->cfg.serial) { block = dim3(32); grid = dim3(1); }
+    else {
+        int bps;
+        switch (nt) {
+            case 1: bps = java ? blocks_per_sm<1, true>() : blocks_per_sm<1, false>(); break;
+            case 2: bps = java ? blocks_per_sm<2, true>() : blocks_per_sm<2, false>(); break;
+            case 3: bps = java ? blocks_per_sm<3, true>() : blocks_per_sm<3, false>(); break;
+            case 4: bps = java ? blocks_per_sm<4, true>() : blocks_per_sm<4, false>(); break;
+            case 6: bps = java ? blocks_per_sm<6, true>() : blocks_per_sm<6, false>(); break;
+            default: bps = java ? blocks_per_sm<8, true>() : blocks_per_sm<8, false>(); break;
+        }
+        int64_t want = (count + 32 * 8 - 1) / (32 * 8);  // blocks if every warp took one batch
+        int64_t full = (int64_t)ctx->sm_count * bps;     // one resident wave
+        grid = dim3((unsigned)(want < full ? (want < 1 ? 1 : want) : full));
+    }
+    const Bijection bij = Bijection::make((uint64_t)count, order_key);
+    ctx->launches++;
+    ctx->updates += count;
+    return java ? launch_update_nt<true>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost)
+                : launch_update_nt<false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
+}
+
+void ge_free_store(ge_ctx* ctx) {
+    cudaFree(ctx->d_W); cudaFree(ctx->d_C); cudaFree(ctx->d_nz); cudaFree(ctx->d_perm); cudaFree(ctx->d_cost);
+    ctx->d_W = ctx->d_C = nullptr; ctx->d_nz = nullptr; ctx->d_perm = nullptr; ctx->d_cost = nullptr;
+    ctx->have_store = false;
+    ctx->h_perm.clear(); ctx->h_perm.shrink_to_fit();
+}
+
+extern "C" int ge_store_init(ge_ctx* ctx) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (ctx->V <= 0) { ctx->err = "no vocabulary: set a graph or import a matrix first"; return GE_ERR_STATE; }
+    const ge_config& c = ctx->cfg;
+    cudaFree(ctx->d_W); cudaFree(ctx->d_C); ctx->d_W = ctx->d_C = nullptr;
+    ctx->D4 = (c.dim + 3) & ~3;
+    ctx->S = (2 * ctx->D4 + 2 + 7) & ~7;
+    const size_t bytes = (size_t)ctx->V * ctx->S * sizeof(float);
+    GE_CUDA(cudaMalloc(&ctx->d_W, bytes));
+    GE_CUDA(cudaMalloc(&ctx->d_C, bytes));
+    store_init<<<(ctx->V + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, ctx->V, c.dim, ctx->D4,
+                                                             ctx->S, c.seed, c.init == GE_INIT_JAVA, 0);
+    GE_CUDA(cudaGetLastError());
+    // stream position after the init draws: the epoch shuffles continue on the same stream
+    // (Optimizer.random and Permutation.random are one thread-local instance)
+    ctx->rng = JavaLcg::seeded(c.seed);
+    ctx->rng.jump((uint64_t)ctx->V * (2 + 2 * (uint64_t)c.dim));
+    ctx->h_perm.clear();
+    ctx->epoch = 0;
+    ctx->history.clear();
+    ctx->have_store = true;
+    return GE_OK;
+}
+
+int ge_train_prepare(ge_ctx* ctx) {
+    if (!ctx->have_cooc || ctx->nnz <= 0) { ctx->err = "no co-occurrence matrix: build or import one first"; return GE_ERR_STATE; }
+    if (!ctx->have_store) { int r = ge_store_init(ctx); if (r) return r; }
+    const ge_config& c = ctx->cfg;
+    if (!ctx->d_nz) {
+        GE_CUDA(cudaMalloc(&ctx->d_nz, (size_t)ctx->nnz * sizeof(NzEntry)));
+        pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
+                                                                 c.math == GE_MATH_JAVA, ctx->xmax, ctx->d_nz);
+        GE_CUDA(cudaGetLastError());
+    }
+    if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
+    if (c.order == GE_ORDER_JAVA) {
+        if (ctx->nnz > 0x7fffffffLL) { ctx->err = "GE_ORDER_JAVA needs nnz < 2^31 (the reference indexes with int)"; return GE_ERR_INVALID; }
+        if (ctx->h_perm.empty()) {
+            ctx->h_perm.resize(ctx->nnz);
+            for (int64_t k = 0; k < ctx->nnz; k++) ctx->h_perm[k] = (int32_t)k;  // Permutation.java:11-15
+        }
+        if (!ctx->d_perm) GE_CUDA(cudaMalloc(&ctx->d_perm, (size_t)ctx->nnz * sizeof(int32_t)));
+    }
+    return GE_OK;
+}
+
+extern "C" int ge_train_epoch(ge_ctx* ctx, double* cost) {
+    if (!ctx) return GE_ERR_INVALID;
+    int r = ge_train_prepare(ctx);
+    if (r) return r;
+    const ge_config& c = ctx->cfg;
+    const int32_t* perm = nullptr;
+    if (c.order == GE_ORDER_JAVA) {
+        // coMatrix.shuffle() (Optimizer.java:79): cumulative Fisher-Yates, ExtendedRandom.java:398-407
+        const int32_t n = (int32_t)ctx->nnz;
+        int32_t* a = ctx->h_perm.data();
+        for (int32_t i = 0; i < n; i++) {
+            const int32_t rr = i + ctx->rng.nextInt(n - i);
+            const int32_t t = a[i]; a[i] = a[rr]; a[rr] = t;
+        }
+        GE_CUDA(cudaMemcpyAsync(ctx->d_perm, a, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+        perm = ctx->d_perm;
+    }
+    GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), ctx->stream));
+    GE_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+    r = ge_launch_update(ctx, ctx->d_nz, ctx->nnz, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
+                         ctx->d_cost, ctx->stream);
+    if (r) return r;
+    GE_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+    double total = 0;
+    GE_CUDA(cudaMemcpyAsync(&total, ctx->d_cost, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    GE_CUDA(cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->update_seconds += ms * 1e-3;
+    const double local = total / (double)ctx->nnz;  // Optimizer.java:96
+    ctx->history.push_back(local);
+    ctx->epoch++;
+    if (cost) *cost = local;
+    return GE_OK;
+}
+
+extern "C" int ge_train(ge_ctx* ctx, ge_epoch_cb cb, void* user, double* final_cost, int32_t* epochs) {
+    if (!ctx) return GE_ERR_INVALID;
+    // Optimizer.optimize :67-120
+    double finalCost = 0, prevCost = 0;
+    int32_t it = 0;
+    for (; it < ctx->cfg.maxiter; it++) {
+        double local = 0;
+        const double before = ctx->update_seconds;
+        int r = ge_train_epoch(ctx, &local);
+        if (r) return r;
+        const double diff = fabs(prevCost - local);  // :98
+        prevCost = local;                             // :102
+        const bool stop = cb && cb(user, it, local, ctx->update_seconds - before);
+        if (diff <= ctx->cfg.tolerance) { finalCost = local; it++; break; }  // :104-107
+        if (stop) { it++; break; }
+    }
+    if (final_cost) *final_cost = finalCost;
+    if (epochs) *epochs = it;
+    return GE_OK;
+}
+
+extern "C" int ge_cost_history(ge_ctx* ctx, double* out, int32_t cap) {
+    if (!ctx) return GE_ERR_INVALID;
+    const int32_t n = (int32_t)ctx->history.size();
+    for (int32_t k = 0; k < n && k < cap; k++) out[k] = ctx->history[k];
+    return n;
+}
+
+template <typename T>
+static int extract_impl(ge_ctx* ctx, T* out) {
+    if (!ctx || !out) return GE_ERR_INVALID;
+    if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
+    const size_t n = (size_t)ctx->V * ctx->cfg.dim;
+    T* d = nullptr;
+    GE_CUDA(cudaMalloc(&d, n * sizeof(T)));
+    extract_avg<T><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, ctx->V, ctx->cfg.dim, ctx->S, d);
+    cudaError_t e = cudaMemcpyAsync(out, d, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    GE_CUDA(e);
+    return GE_OK;
+}
+extern "C" int ge_extract(ge_ctx* ctx, double* out) { return extract_impl<double>(ctx, out); }
+extern "C" int ge_extract_f32(ge_ctx* ctx, float* out) { return extract_impl<float>(ctx, out); }
+
+extern "C" int ge_store_export(ge_ctx* ctx, int32_t which, float* out) {
+    if (!ctx || !out || which < 0 || which > 7) return GE_ERR_INVALID;
+    if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
+    const int32_t dim = ctx->cfg.dim, D4 = ctx->D4;
+    const float* A = (which & 1) ? ctx->d_C : ctx->d_W;
+    int32_t off, width;
+    switch (which >> 1) {
+        case 0: off = 0; width = dim; break;            // focus / context
+        case 1: off = 2 * D4; width = 1; break;         // fBias / cBias
+        case 2: off = D4; width = dim; break;           // gradSqFocus / gradSqContext
+        default: off = 2 * D4 + 1; width = 1; break;    // gradSqFBias / gradSqCBias
+    }
+    const size_t n = (size_t)ctx->V * width;
+    float* d = nullptr;
+    GE_CUDA(cudaMalloc(&d, n * sizeof(float)));
+    store_component<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(A, ctx->V, dim, ctx->S, off, width, d);
+    cudaError_t e = cudaMemcpyAsync(out, d, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    GE_CUDA(e);
+    return GE_OK;
+}
+
+extern "C" int ge_epoch_order(ge_ctx* ctx, int32_t epoch, int32_t* perm, int64_t cap) {
+    if (!ctx || !perm) return GE_ERR_INVALID;
+    if (!ctx->have_cooc || cap < ctx->nnz || ctx->nnz > 0x7fffffffLL) { ctx->err = "bad capacity / no matrix"; return GE_ERR_INVALID; }
+    if (ctx->cfg.order == GE_ORDER_JAVA) {
+        if (ctx->h_perm.empty()) { ctx->err = "GE_ORDER_JAVA: order exists only after an epoch has run"; return GE_ERR_STATE; }
+        for (int64_t k = 0; k < ctx->nnz; k++) perm[k] = ctx->h_perm[k];
+        return GE_OK;
+    }
+    int32_t* d = nullptr;
+    GE_CUDA(cudaMalloc(&d, (size_t)ctx->nnz * sizeof(int32_t)));
+    materialise_order<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(Bijection::make((uint64_t)ctx->nnz, epoch_key(ctx->cfg.seed, epoch)), ctx->nnz, d);
+    cudaError_t e = cudaMemcpyAsync(perm, d, (size_t)ctx->nnz * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    GE_CUDA(e);
+    return GE_OK;
+}
+
+extern "C" int ge_train_stats(ge_ctx* ctx, double* update_seconds, int64_t* launches, int64_t* updates) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (update_seconds) *update_seconds = ctx->update_seconds;
+    if (launches) *launches = ctx->launches;
+    if (updates) *updates = ctx->updates;
+    return GE_OK;
+}

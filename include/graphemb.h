@@ -1,0 +1,142 @@
+/* graphemb.h — C ABI of libgraphemb.so, the B200-native hot path of Phaken/graph-embeddings.
+ *
+ * The reference has no FFI layer; its seam is two Java interfaces consumed by
+ * Main.runProgram (J/Main.java:70-77, J = src/main/java/org/uu/nl/embedding/):
+ *     CoOccurrenceMatrix  (J/util/CoOccurrenceMatrix.java:6-16)  <- new BookmarkColoring(graph, config)
+ *     IOptimizer/Optimum  (J/opt/IOptimizer.java:6-11, J/opt/Optimum.java:9-41) <- optimizer.optimize()
+ * Each entry point below names the reference code it replaces.  INTEGRATION.md shows the
+ * Java-side binding (JNI for the Java 8 target of pom.xml:13-14, Panama FFM on JDK >= 22).
+ *
+ * Conventions: plain C, opaque handle, caller-owned buffers, int status (0 = OK, negative =
+ * error, text via ge_last_error).  Never throws, never aborts, never keeps a caller pointer
+ * after return.  One call at a time per handle.  Callbacks run on the calling thread.
+ * All host pointers are ordinary host memory unless a function says "device".
+ */
+#ifndef GRAPHEMB_H
+#define GRAPHEMB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GE_OK 0
+#define GE_ERR_INVALID (-1)   /* bad argument / configuration (Configuration.check, :478-494) */
+#define GE_ERR_STATE (-2)     /* call order violated (e.g. train before a matrix exists)       */
+#define GE_ERR_CUDA (-3)      /* CUDA runtime error; message has the cudaError string          */
+#define GE_ERR_NOMEM (-4)     /* device or host allocation failed                              */
+#define GE_ERR_GRAPH (-5)     /* neighbour lists not sorted/unique, ids out of range           */
+#define GE_ERR_DIST (-6)      /* NCCL / multi-GPU set-up failure                               */
+#define GE_ERR_NODEVICE (-7)  /* no CUDA device: there is NO CPU fallback                      */
+
+/* Configuration.EmbeddingMethod (J/util/config/Configuration.java:19-21) */
+enum { GE_METHOD_GLOVE = 0, GE_METHOD_PGLOVE = 1 };
+/* Configuration.OptimizationMethod (:23-25); only ADAGRAD is on the hot path this round */
+enum { GE_OPT_ADAGRAD = 0 };
+/* Configuration.BCANormalization (:31-33) */
+enum { GE_NORM_NONE = 0, GE_NORM_UNITY = 1, GE_NORM_COUNTS = 2 };
+/* Arithmetic of the AdaGrad step.
+ * GE_MATH_FAST : f32 arithmetic (rsqrt), one warp per nonzero, Hogwild across warps — the
+ *                throughput path.
+ * GE_MATH_JAVA : the reference's exact promotion pattern (fp64 divide/sqrt/log/pow islands,
+ *                J/opt/grad/Adagrad.java:58-93).  With ge_config.serial = 1 it runs one warp
+ *                in the reference's single-thread order (the parity trajectory). */
+enum { GE_MATH_FAST = 0, GE_MATH_JAVA = 1 };
+/* Epoch order.  GE_ORDER_JAVA replays java.util.Random's cumulative Fisher-Yates on the host
+ * (J/util/rnd/Permutation.java:21-23, ExtendedRandom.java:398-407); GE_ORDER_DEVICE uses a
+ * keyed bijection evaluated on the device (no permutation array). */
+enum { GE_ORDER_DEVICE = 0, GE_ORDER_JAVA = 1 };
+/* Store initialisation.  GE_INIT_JAVA replays the LCG stream of Optimizer.java:50-57 bit for
+ * bit (on the device, by LCG jump-ahead); GE_INIT_COUNTER is a counter-based generator with
+ * the same distribution (U[0,1)-0.5)/dim. */
+enum { GE_INIT_COUNTER = 0, GE_INIT_JAVA = 1 };
+
+typedef struct ge_config {
+    int32_t dim;           /* Configuration.dim                                   */
+    int32_t method;        /* GE_METHOD_*   <- Configuration.method               */
+    int32_t opt_method;    /* GE_OPT_*      <- Configuration.opt.method           */
+    int32_t directed;      /* bca.directed (reverse pass is implied when directed) */
+    int32_t normalize;     /* GE_NORM_*     <- bca.normalize                      */
+    double alpha;          /* bca.alpha                                           */
+    double epsilon;        /* bca.epsilon                                         */
+    double tolerance;      /* opt.tolerance                                       */
+    int32_t maxiter;       /* opt.maxiter                                         */
+    int64_t seed;          /* reference: System.currentTimeMillis() (Main.java:62) */
+    float learning_rate;   /* hard-wired 0.05f in Optimizer.java:26; 0 -> 0.05f   */
+    int32_t math;          /* GE_MATH_*                                           */
+    int32_t order;         /* GE_ORDER_*                                          */
+    int32_t init;          /* GE_INIT_*                                           */
+    int32_t serial;        /* 1: single warp, reference single-thread order       */
+    int32_t device;        /* CUDA device ordinal                                 */
+} ge_config;
+
+typedef struct ge_ctx ge_ctx;
+
+/* per-epoch progress (Optimizer.java:97-101): return non-zero to stop early */
+typedef int (*ge_epoch_cb)(void* user, int32_t epoch, double cost, double seconds);
+
+/* fills *cfg with the reference defaults of the shipped configs (pglove? no: glove, d=300 is
+ * the caller's business) — alpha .1, eps 1e-3, directed, adagrad, tol 1e-4, maxiter 1000 */
+void ge_config_default(ge_config* cfg);
+
+int ge_create(const ge_config* cfg, ge_ctx** out);
+void ge_destroy(ge_ctx* ctx);
+const char* ge_last_error(const ge_ctx* ctx); /* ctx may be NULL: last create error */
+const char* ge_version(void);
+
+/* A1 — adjacency hand-off (BookmarkColoring.java:49-52).  Neighbour lists must be sorted by
+ * id and unique; off arrays have V+1 entries.  Copies to the device. */
+int ge_set_graph_csr(ge_ctx*, int32_t V, const int64_t* out_off, const int32_t* out_nbr,
+                     const float* out_w, const int64_t* in_off, const int32_t* in_nbr,
+                     const float* in_w);
+
+/* A2-A4 — new BookmarkColoring(graph, config): builds the COO on the device.
+ * Outputs: nnz = coOccurrenceCount(), xmax = max().  Rows [first, first+count) only when
+ * count >= 0 (multi-GPU row sharding); count < 0 = all rows. */
+int ge_cooc_build(ge_ctx*, int64_t* nnz, double* xmax);
+int ge_cooc_build_rows(ge_ctx*, int32_t first, int32_t count, int64_t* nnz, double* xmax);
+/* counters of the last build: pops (pair events), scanned adjacency entries, seconds on device */
+int ge_cooc_stats(ge_ctx*, int64_t* pops, int64_t* scanned, double* seconds);
+
+/* A6 — cIdx_I/J/C for all k (unpermuted); cap = capacity of the three arrays. */
+int ge_cooc_export(ge_ctx*, int32_t* I, int32_t* J, float* X, int64_t cap);
+/* feed an external COO (validation; C5-style direct COO).  xmax <= 0: computed. */
+int ge_cooc_import(ge_ctx*, int32_t V, int64_t nnz, const int32_t* I, const int32_t* J,
+                   const float* X, double xmax);
+int64_t ge_cooc_count(ge_ctx*);   /* coOccurrenceCount() */
+int32_t ge_vocab_size(ge_ctx*);   /* vocabSize() */
+double ge_cooc_max(ge_ctx*);      /* max() */
+
+/* B1 — allocate + initialise the embedding store (Optimizer ctor :45-57, Adagrad ctor :22-33).
+ * Called implicitly by ge_train when missing. */
+int ge_store_init(ge_ctx*);
+/* B4/B5 — one epoch: shuffle + all nonzeros; cost = localCost (Optimizer.java:79-96). */
+int ge_train_epoch(ge_ctx*, double* cost);
+/* B6 — optimizer.optimize(): epoch loop with the tolerance stop rule (:67-120). */
+int ge_train(ge_ctx*, ge_epoch_cb cb, void* user, double* final_cost, int32_t* epochs);
+int ge_cost_history(ge_ctx*, double* out, int32_t cap); /* Optimum.costHistory; returns count */
+/* B7 — extractResult(): (focus+context)/2, row-major V x dim. */
+int ge_extract(ge_ctx*, double* out);
+int ge_extract_f32(ge_ctx*, float* out);
+/* raw store rows in the reference's layout (validation): which = 0 focus, 1 context,
+ * 2 fBias, 3 cBias, 4 gradSqFocus, 5 gradSqContext, 6 gradSqFBias, 7 gradSqCBias */
+int ge_store_export(ge_ctx*, int32_t which, float* out);
+/* epoch order used by the last/next epoch as an explicit permutation (validation) */
+int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);
+/* device seconds and kernel launches spent in update kernels so far */
+int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
+
+/* --- multi-GPU (one process per GPU) ------------------------------------ */
+#define GE_NCCL_ID_BYTES 128
+/* rank 0 creates the id, the host distributes it (torch.distributed / file / env) */
+int ge_dist_unique_id(void* id128);
+int ge_dist_init(ge_ctx*, int32_t rank, int32_t world, const void* id128);
+/* block grid: nblocks x nblocks (8 x 8 in the north star); bucket the local COO rows */
+int ge_dist_prepare(ge_ctx*, int32_t nblocks);
+int ge_dist_train_epoch(ge_ctx*, double* cost);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPHEMB_H */

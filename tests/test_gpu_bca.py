@@ -1,0 +1,113 @@
+"""GPU co-occurrence builder vs the CPU oracle: bit-exact (i,j) set, bit-equal f32 values, equal
+max / nnz / pop counts.  Calls go through the C ABI (graph_embeddings_b200.api -> libgraphemb.so)."""
+import numpy as np
+import pytest
+
+import oracle
+from graph_embeddings_b200 import BCA, BookmarkColoring, Configuration, GraphEmbError, Opt, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def cfg(alpha=0.1, eps=1e-3, directed=True, normalize=None, dim=8):
+    return Configuration(method="glove", dim=dim, bca=BCA(alpha, eps, directed, normalize), opt=Opt("adagrad", 0, 1))
+
+
+def check(g, alpha=0.1, eps=1e-3, directed=True, normalize=None, exact_values=True):
+    b = BookmarkColoring(g, cfg(alpha, eps, directed, normalize))
+    r = oracle.cooc_build(g, alpha, eps, directed, normalize or "none", threads=8)
+    assert b.coOccurrenceCount() == r.nnz
+    I, J, X = b.coo()
+    o = np.lexsort((J, I))
+    ri, rj, rx = r.sorted()
+    assert np.array_equal(I[o], ri) and np.array_equal(J[o], rj)
+    if exact_values:
+        assert np.array_equal(X[o].view(np.uint32), rx.view(np.uint32))
+    else:
+        assert np.allclose(X[o], rx, rtol=1e-6, atol=0)
+    assert b.max() == r.max
+    s = b.stats()
+    assert s["pops"] == r.pops and s["scanned"] == r.scanned
+    # storage order is row-major by bookmark, discovery order within the row == the oracle's order
+    assert np.array_equal(I, r.I) and np.array_equal(J, r.J)
+    return b, r
+
+
+HAND = {
+    "isolated": ([], 1), "edge": ([(0, 1, 1.0)], None), "two_cycle": ([(0, 1, 1.0), (1, 0, 1.0)], None),
+    "self_loop": ([(0, 0, 1.0)], None), "star": ([(0, 1, 1.0), (0, 2, 0.1)], None),
+    "both_lists": ([(0, 1, 1.0), (1, 0, 0.5)], None), "dangling": ([(0, 1, 1.0), (2, 1, 0.1)], 5),
+}
+
+
+@pytest.mark.parametrize("name", sorted(HAND))
+@pytest.mark.parametrize("directed", [True, False])
+def test_hand_graphs(name, directed):
+    edges, V = HAND[name]
+    check(synth.tiny(edges, V), directed=directed)
+    check(synth.tiny(edges, V), eps=0.25, directed=directed)
+
+
+@pytest.mark.parametrize("directed", [True, False])
+def test_rmat(directed):
+    check(synth.rmat(5000, 40000, 4), directed=directed)
+
+
+def test_rmat_hub_rows_use_global_tier():
+    # small V + dense graph: many rows exceed the 512-record shared-memory table
+    b, r = check(synth.rmat(3000, 60000, 5), eps=1e-4)
+    assert np.diff(r.row_off).max() > 512
+
+
+@pytest.mark.parametrize("gen,kw", [(synth.dblp_like, dict(scale=0.02)), (synth.onstage_like, dict(scale=0.03)),
+                                    (synth.saa_like, dict(scale=0.02))])
+def test_config_shaped_graphs(gen, kw):
+    check(gen(**kw))
+
+
+@pytest.mark.parametrize("normalize", ["counts", "unity"])
+def test_normalisation(normalize):
+    check(synth.rmat(2000, 10000, 6), normalize=normalize)
+    check(synth.tiny([], V=3), normalize=normalize)       # empty rows after root removal -> max 1
+
+
+def test_other_alpha_epsilon():
+    check(synth.rmat(2000, 10000, 7), alpha=0.3, eps=1e-2)
+    check(synth.rmat(1000, 5000, 8), alpha=0.05, eps=1e-4)
+    check(synth.rmat(1000, 5000, 8), eps=2.0)             # root never distributes
+
+
+def test_row_range_build():
+    g = synth.rmat(3000, 20000, 9)
+    r = oracle.cooc_build(g, threads=4)
+    b = BookmarkColoring(g, cfg(), rows=(1000, 500))
+    I, J, X = b.coo()
+    lo, hi = r.row_off[1000], r.row_off[1500]
+    assert np.array_equal(I, r.I[lo:hi]) and np.array_equal(J, r.J[lo:hi]) and np.array_equal(X, r.X[lo:hi])
+
+
+def test_rejects_unsorted_or_duplicate_neighbours():
+    g = synth.tiny([(0, 1, 1.0), (0, 2, 1.0)])
+    g.out_nbr = g.out_nbr[::-1].copy()
+    with pytest.raises(GraphEmbError) as e:
+        BookmarkColoring(g, cfg())
+    assert e.value.code == -5
+
+
+def test_size_independent_properties_at_scale():
+    # C1-sized graph (V=320k): no oracle run; check invariants the domain offers
+    g = synth.dblp_like(1.0)
+    b = BookmarkColoring(g, cfg())
+    I, J, X = b.coo()
+    assert b.coOccurrenceCount() == len(I) and np.all(np.diff(I) >= 0)
+    key = I.astype(np.int64) * g.V + J
+    assert len(np.unique(key)) == len(key)                        # one entry per (i, j)
+    diag = X[I == J]
+    assert len(diag) == g.V and np.all(diag >= np.float32(0.1) + np.float32(0.1))   # fwd + rev root keep
+    rowsum = np.bincount(I, weights=X.astype(np.float64), minlength=g.V)
+    assert rowsum.max() <= 2.0 + 1e-5 and X.min() > 0             # paint is conserved per pass
+    assert b.max() == float(X.max())
+    # sampled rows against the oracle
+    r = oracle.cooc_build(g, first=12345, count=2000, threads=8)
+    off = np.searchsorted(I, [12345, 14345])
+    assert np.array_equal(J[off[0]:off[1]], r.J) and np.array_equal(X[off[0]:off[1]], r.X)

@@ -1,0 +1,132 @@
+"""GPU trainer vs the CPU oracle through the C ABI."""
+import numpy as np
+import pytest
+
+import oracle
+from graph_embeddings_b200 import (BCA, BookmarkColoring, Configuration, GraphEmbError, ImportedMatrix, Opt,
+                                   createOptimizer, synth)
+
+pytestmark = pytest.mark.gpu
+STORE = ["focus", "context", "fBias", "cBias", "gsFocus", "gsContext", "gsFBias", "gsCBias"]
+
+
+def cfg(method="glove", dim=16, maxiter=3, tol=0.0, **kw):
+    return Configuration(method=method, dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", tol, maxiter), **kw)
+
+
+def random_coo(V, nnz, seed):
+    rng = np.random.default_rng(seed)
+    return (rng.integers(0, V, nnz).astype(np.int32), rng.integers(0, V, nnz).astype(np.int32),
+            rng.uniform(1e-3, 0.4, nnz).astype(np.float32))
+
+
+@pytest.mark.parametrize("dim", [5, 16, 100, 128, 300])
+def test_store_init_replays_java_stream(dim):
+    V = 3000
+    I, J, X = random_coo(V, 100, 1)
+    c = cfg(dim=dim, seed=424242)
+    m = ImportedMatrix(V, I, J, X, c)
+    opt = createOptimizer(c, m)
+    t = oracle.Trainer(V, I, J, X, float(X.max()), dim, "glove", 424242)
+    for name in STORE:
+        assert np.array_equal(opt.store(name), t.store(name)), name
+    assert np.array_equal(opt.extractResult(), t.extract())
+
+
+def test_epoch_order_java_matches_fisher_yates_replay():
+    V, dim = 500, 8
+    I, J, X = random_coo(V, 5000, 2)
+    c = cfg(dim=dim, seed=99, order="java", math="java", serial=True)
+    m = ImportedMatrix(V, I, J, X, c)
+    opt = createOptimizer(c, m)
+    t = oracle.Trainer(V, I, J, X, float(X.max()), dim, "glove", 99)
+    for ep in range(3):
+        opt.epoch(); t.epoch()
+        assert np.array_equal(opt.epoch_order(ep), t.get_perm())
+
+
+def test_device_order_is_a_fresh_permutation_each_epoch():
+    V = 100
+    for nnz in (1, 2, 3, 1000, 4097, 65536):
+        I, J, X = random_coo(V, nnz, 3)
+        c = cfg(dim=4)
+        m = ImportedMatrix(V, I, J, X, c)
+        opt = createOptimizer(c, m)
+        p0, p1 = opt.epoch_order(0), opt.epoch_order(1)
+        assert np.array_equal(np.sort(p0), np.arange(nnz)) and np.array_equal(np.sort(p1), np.arange(nnz))
+        if nnz > 100:
+            assert not np.array_equal(p0, p1)
+
+
+@pytest.mark.parametrize("method", ["glove", "pglove"])
+@pytest.mark.parametrize("dim", [10, 128, 300])
+def test_serial_java_mode_tracks_single_thread_reference(method, dim):
+    """One warp, reference order, reference promotion pattern: agrees with the 1-thread oracle to
+    a few ulp (only the warp-tree dot product and CUDA's log/pow differ)."""
+    V, nnz = 300, 4000
+    I, J, X = random_coo(V, nnz, 4)
+    c = cfg(method=method, dim=dim, seed=5, order="java", math="java", serial=True)
+    m = ImportedMatrix(V, I, J, X, c, xmax=float(X.max()))
+    opt = createOptimizer(c, m)
+    t = oracle.Trainer(V, I, J, X, float(X.max()), dim, method, 5)
+    for ep in range(3):
+        cg, co = opt.epoch(), t.epoch()
+        assert abs(cg - co) <= 1e-5 * abs(co), (ep, cg, co)
+    for name in STORE:
+        a, b = opt.store(name), t.store(name)
+        assert np.allclose(a, b, rtol=2e-4, atol=2e-6), name
+    assert np.allclose(opt.extractResult(), t.extract(), rtol=2e-4, atol=2e-6)
+
+
+def _nn_overlap(A, B, sample, k=10):
+    def topk(E):
+        En = E / np.maximum(np.linalg.norm(E, axis=1, keepdims=True), 1e-12)
+        S = En[sample] @ En.T
+        S[np.arange(len(sample)), sample] = -np.inf
+        return np.argsort(-S, axis=1)[:, :k]
+    a, b = topk(A), topk(B)
+    return np.mean([len(set(x) & set(y)) / k for x, y in zip(a, b)])
+
+
+@pytest.mark.parametrize("method", ["glove", "pglove"])
+def test_fast_hogwild_loss_within_1pct_and_nn_overlap(method):
+    """north_star bars: per-epoch loss within 1 % of the single-thread reference run, top-10
+    nearest-neighbour overlap >= 0.9 on the final embeddings."""
+    g = synth.rmat(20000, 160000, 4)
+    dim, epochs = 64, 12
+    c = cfg(method=method, dim=dim, maxiter=epochs, seed=31)
+    bca = BookmarkColoring(g, c)
+    I, J, X = bca.coo()
+    if method == "pglove":
+        assert X.max() < 1.0
+    opt = createOptimizer(c, bca).optimize()
+    t = oracle.Trainer(g.V, I, J, X, bca.max(), dim, method, 31)
+    hist, _ = t.optimize(epochs, 0.0)
+    got = np.array(opt.costHistory)
+    rel = np.abs(got - hist) / hist
+    assert len(got) == epochs and rel.max() < 0.01, rel
+    sample = np.random.default_rng(0).choice(g.V, 1000, replace=False)
+    ov = _nn_overlap(opt.getResult(), t.extract(), sample)
+    assert ov >= 0.9, ov
+
+
+def test_optimize_stop_rule_matches_reference():
+    V, dim = 200, 8
+    I, J, X = random_coo(V, 3000, 6)
+    c = cfg(dim=dim, maxiter=5, tol=1e9)
+    opt = createOptimizer(c, ImportedMatrix(V, I, J, X, c)).optimize()
+    assert len(opt.costHistory) == 1 and opt.getFinalCost() == opt.costHistory[0]
+    c = cfg(dim=dim, maxiter=4, tol=0.0)
+    opt = createOptimizer(c, ImportedMatrix(V, I, J, X, c)).optimize()
+    assert len(opt.costHistory) == 4 and opt.getFinalCost() == 0.0       # Optimizer.java:73
+
+
+def test_errors():
+    with pytest.raises(ValueError):
+        cfg(method="bogus").to_native()
+    c = cfg()
+    c.opt.method = "adam"
+    with pytest.raises(ValueError):
+        createOptimizer(c, None)
+    with pytest.raises(GraphEmbError):
+        ImportedMatrix(0, [0], [0], [0.1], cfg())
