@@ -18,6 +18,7 @@ NORM = {"none": 0, "unity": 1, "counts": 2}
 MATH = {"fast": 0, "java": 1}
 ORDER = {"device": 0, "java": 1}
 INIT = {"counter": 0, "java": 1}
+UPDATE = {"atomic": 0, "store": 1}
 NCCL_ID_BYTES = 128
 
 
@@ -27,7 +28,7 @@ class GeConfig(C.Structure):
                 ("epsilon", C.c_double), ("tolerance", C.c_double), ("maxiter", C.c_int32),
                 ("seed", C.c_int64), ("learning_rate", C.c_float), ("math", C.c_int32),
                 ("order", C.c_int32), ("init", C.c_int32), ("serial", C.c_int32),
-                ("device", C.c_int32)]
+                ("device", C.c_int32), ("update", C.c_int32)]
 
 
 EPOCH_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_double, C.c_double)

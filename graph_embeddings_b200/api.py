@@ -65,6 +65,7 @@ class Configuration:
     math: str = "fast"
     order: str = "device"
     init: str = "java"
+    update: str = "atomic"
     serial: bool = False
     device: int = 0
     extra: dict = field(default_factory=dict)
@@ -101,6 +102,7 @@ class Configuration:
         c.seed = self.seed
         c.math, c.order, c.init = _lib.MATH[self.math], _lib.ORDER[self.order], _lib.INIT[self.init]
         c.serial, c.device = int(self.serial), self.device
+        c.update = _lib.UPDATE[self.update]
         return c
 
 

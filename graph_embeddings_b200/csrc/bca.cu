@@ -74,6 +74,7 @@ struct Table {
     float* accr;     // BCV value, reverse pass
     uint8_t* flg;    // bit0: popped in fwd, bit1: popped in rev
     HT* hash;        // record index + 1, 0 = empty
+    HT* ord;         // record indices in first-pop order (= the order BCV entries are created)
     int32_t cap;
     uint32_t hshift, hmask;
 
@@ -100,7 +101,7 @@ struct Table {
 // Runs one pass (DirectedWeighted.doWork with reverse = (pass==1), or UndirectedWeighted.doWork)
 // on table T holding n records; returns the new n, or -1 on table overflow.
 template <typename HT>
-__device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int lane,
+__device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int lane, int& npop,
                         unsigned long long& pops, unsigned long long& scanned) {
     const unsigned FULL = 0xffffffffu;
     const uint8_t bit = (uint8_t)(1 << pass);
@@ -118,8 +119,10 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
         const int idx = __shfl_sync(FULL, bidx, __ffs(who) - 1);
         const int32_t focus = (int32_t)m;
         const double paint = T.wet[idx];
+        const bool first_pop = T.flg[idx] == 0;
         __syncwarp();
         if (lane == 0) {
+            if (first_pop) T.ord[npop] = (HT)idx;
             T.wet[idx] = 0.0;
             T.key[idx] = m | INACTIVE;
             // bcv.add(focusNode, alpha * wetPaint) (:53) -> BCV.add(int,float) :35-37
@@ -130,6 +133,7 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
             T.flg[idx] = f | bit;
         }
         pops++;
+        npop += first_pop ? 1 : 0;
         __syncwarp();
         if (paint < P.eps) continue;  // :56
         const double base = __dmul_rn(P.one_minus_alpha, paint);
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
     {
         uint8_t* p;
         if (SMEM) {
-            const size_t per = (size_t)P.cap * (8 + 4 + 4 + 4 + 1) + (size_t)hcap * sizeof(HT);
+            const size_t per = (size_t)P.cap * (8 + 4 + 4 + 4 + 1 + sizeof(HT)) + (size_t)hcap * sizeof(HT);
             p = smem + (size_t)wib * ((per + 15) & ~(size_t)15);
         } else {
             const size_t gw = (size_t)blockIdx.x * (blockDim.x >> 5) + wib;
@@ -209,6 +213,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         T.accf = reinterpret_cast<float*>(p); p += (size_t)P.cap * 4;
         T.accr = reinterpret_cast<float*>(p); p += (size_t)P.cap * 4;
         T.hash = reinterpret_cast<HT*>(p); p += (size_t)hcap * sizeof(HT);
+        T.ord = reinterpret_cast<HT*>(p); p += (size_t)P.cap * sizeof(HT);
         T.flg = p;
         T.cap = P.cap; T.hshift = 32 - P.hcap_log2; T.hmask = hcap - 1;
     }
@@ -233,11 +238,12 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         }
         __syncwarp();
         unsigned long long bp = 0, bs = 0;
-        int n = bca_pass(P, T, 1, 0, lane, bp, bs);
+        int npop = 0;
+        int n = bca_pass(P, T, 1, 0, lane, npop, bp, bs);
         if (n > 0 && P.directed) {  // BCAJob.call :32-36 — reverse pass, merged below
             if (lane == 0) { T.key[0] = (uint32_t)bookmark; T.wet[0] = 1.0; }
             __syncwarp();
-            n = bca_pass(P, T, n, 1, lane, bp, bs);
+            n = bca_pass(P, T, n, 1, lane, npop, bp, bs);
         }
         if (n < 0) {  // table overflow: hand the bookmark to the next tier
             if (lane == 0) P.overflow[atomicAdd(P.n_overflow, 1)] = bookmark;
@@ -249,7 +255,8 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
 
         // ---- BCV.merge (:105-107): fwd + rev per key; then normalise (BookmarkColoring.java:81-91)
         // value of record r:
-        auto value = [&](int r) -> float {
+        auto value = [&](int q) -> float {  // q-th BCV entry in creation order
+            const int r = (int)T.ord[q];
             const uint8_t f = T.flg[r];
             if (!P.directed) return T.accf[r];
             return (f == 3) ? __fadd_rn(T.accf[r], T.accr[r]) : ((f & 1) ? T.accf[r] : T.accr[r]);
@@ -290,7 +297,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
             if (start >= 0) {
                 const long long o = start + (r - first_out);
                 P.aI[o] = bookmark;
-                P.aJ[o] = (int32_t)(T.key[r] & ~INACTIVE);
+                P.aJ[o] = (int32_t)(T.key[T.ord[r]] & ~INACTIVE);
                 P.aX[o] = v;
             }
         }
@@ -433,7 +440,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
 
     // tier-1 launch geometry
     const int hcap1_log2 = 10;  // 1024 slots for 512 records
-    const size_t per1 = (((size_t)T1_CAP * 21 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
+    const size_t per1 = (((size_t)T1_CAP * 23 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
     const size_t smem1 = per1 * T1_WARPS;
     GE_CUDA(cudaFuncSetAttribute(bca_push<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     int bps1 = 1;
@@ -485,7 +492,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
             overflow_rows += n_over;
             int hl = 1;
             while (((int64_t)1 << hl) < 2 * cap2) hl++;
-            const size_t per2 = (((size_t)cap2 * 21 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
+            const size_t per2 = (((size_t)cap2 * 25 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
             int64_t warps = (int64_t)ctx->sm_count * 16;
             if (warps > n_over) warps = n_over;
             size_t fb = 0, tb = 0;

@@ -17,6 +17,14 @@ namespace {
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
+// vector float reduction at L2 (sm_90+): no value returns to the SM, updates are never lost
+__device__ __forceinline__ void red4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red2(float* p, float a, float b) {
+    asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -61,7 +69,7 @@ struct Bijection {
 // K6 — the update kernel.  NT = float4 chunks per lane per vector (dim <= 128*NT).
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
-template <int NT, bool JAVA>
+template <int NT, bool JAVA, bool ATOMIC>
 __global__ void __launch_bounds__(256)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
@@ -161,6 +169,13 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                             cv[e] = (float)__dsub_rn((double)cv[e], __dmul_rn(__ddiv_rn((double)g2, __dsqrt_rn((double)gcv[e])), lr_d));
                             gwv[e] = __fadd_rn(gwv[e], __fmul_rn(g1, g1));
                             gcv[e] = __fadd_rn(gcv[e], __fmul_rn(g2, g2));
+                        } else if (ATOMIC) {  // deltas, applied by the L2 with red.add
+                            const float g1 = wc * cv[e];
+                            const float g2 = wc * wv[e];
+                            wv[e] = -g1 * rsqrtf(gwv[e]) * lr;
+                            cv[e] = -g2 * rsqrtf(gcv[e]) * lr;
+                            gwv[e] = g1 * g1;
+                            gcv[e] = g2 * g2;
                         } else {
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
@@ -170,10 +185,17 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                             gcv[e] += g2 * g2;
                         }
                     }
-                    st4(wrow + 4 * ch, w[q]);
-                    st4(crow + 4 * ch, c[q]);
-                    st4(wrow + D4 + 4 * ch, gw[q]);
-                    st4(crow + D4 + 4 * ch, gc[q]);
+                    if (ATOMIC) {
+                        red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
+                        red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
+                        red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
+                        red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
+                    } else {
+                        st4(wrow + 4 * ch, w[q]);
+                        st4(crow + 4 * ch, c[q]);
+                        st4(wrow + D4 + 4 * ch, gw[q]);
+                        st4(crow + D4 + 4 * ch, gc[q]);
+                    }
                 }
             }
             if (lane == 0) {  // Adagrad.java:88-93 — bias step has no learning rate
@@ -183,14 +205,19 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     const float w2 = __fmul_rn(wc, wc);
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
+                } else if (ATOMIC) {
+                    red2(wrow + 2 * D4, -wc * rsqrtf(bw.y), wc * wc);
+                    red2(crow + 2 * D4, -wc * rsqrtf(bc.y), wc * wc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
                     bw.y += wc * wc;
                     bc.y += wc * wc;
                 }
-                *reinterpret_cast<float2*>(wrow + 2 * D4) = bw;
-                *reinterpret_cast<float2*>(crow + 2 * D4) = bc;
+                if (!ATOMIC || JAVA) {
+                    *reinterpret_cast<float2*>(wrow + 2 * D4) = bw;
+                    *reinterpret_cast<float2*>(crow + 2 * D4) = bc;
+                }
             }
             if (JAVA) __syncwarp();  // serial order: lane 0's bias store precedes the next loads
         }
@@ -304,13 +331,13 @@ uint64_t epoch_key(int64_t seed, int32_t epoch) {
 // ==========================================================================================
 // host side
 // ==========================================================================================
-template <bool JAVA>
+template <bool JAVA, bool ATOMIC>
 static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStream_t st,
                             const NzEntry* nz, int64_t count, float* W, float* C,
                             const int32_t* perm, Bijection bij, double* d_cost) {
     const ge_config& c = ctx->cfg;
 #define GE_LAUNCH(NT_)                                                                            \
-    glove_adagrad_update<NT_, JAVA><<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4,  \
+    glove_adagrad_update<NT_, JAVA, ATOMIC><<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4,  \
                                                             ctx->S, c.method, ctx->xmax,         \
                                                             c.learning_rate, d_cost)
     switch (nt) {
@@ -330,7 +357,7 @@ static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStre
 template <int NT, bool JAVA>
 static int blocks_per_sm() {
     int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, glove_adagrad_update<NT, JAVA>, 256, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, glove_adagrad_update<NT, JAVA, !JAVA>, 256, 0);
     return n < 1 ? 1 : n;
 }
 
@@ -360,8 +387,10 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
     const Bijection bij = Bijection::make((uint64_t)count, order_key);
     ctx->launches++;
     ctx->updates += count;
-    return java ? launch_update_nt<true>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost)
-                : launch_update_nt<false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
+    if (java) return launch_update_nt<true, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
+    if (ctx->cfg.update == GE_UPDATE_STORE)
+        return launch_update_nt<false, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
+    return launch_update_nt<false, true>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
 }
 
 void ge_free_store(ge_ctx* ctx) {

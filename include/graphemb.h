@@ -52,6 +52,13 @@ enum { GE_ORDER_DEVICE = 0, GE_ORDER_JAVA = 1 };
  * the same distribution (U[0,1)-0.5)/dim. */
 enum { GE_INIT_COUNTER = 0, GE_INIT_JAVA = 1 };
 
+/* How the FAST path writes a row back.  GE_UPDATE_ATOMIC: deltas are applied with vector
+ * red.global.add.f32 at the L2 — concurrent warps on one hub row never lose each other's
+ * update (only the gradient is stale, as in the reference's own Hogwild threads).
+ * GE_UPDATE_STORE: plain read-modify-write stores, exactly the reference's racy pattern
+ * (Adagrad.java:76-80) but with thousands of warps instead of nproc-1 threads. */
+enum { GE_UPDATE_ATOMIC = 0, GE_UPDATE_STORE = 1 };
+
 typedef struct ge_config {
     int32_t dim;           /* Configuration.dim                                   */
     int32_t method;        /* GE_METHOD_*   <- Configuration.method               */
@@ -69,6 +76,7 @@ typedef struct ge_config {
     int32_t init;          /* GE_INIT_*                                           */
     int32_t serial;        /* 1: single warp, reference single-thread order       */
     int32_t device;        /* CUDA device ordinal                                 */
+    int32_t update;        /* GE_UPDATE_*                                         */
 } ge_config;
 
 typedef struct ge_ctx ge_ctx;
