@@ -41,6 +41,7 @@ SIGNATURES = {
     "ge_destroy": (None, [_P]),
     "ge_last_error": (C.c_char_p, [_P]),
     "ge_version": (C.c_char_p, []),
+    "ge_set_stream": (C.c_int, [_P, _P]),
     "ge_set_graph_csr": (C.c_int, [_P, _I32, _P, _P, _P, _P, _P, _P]),
     "ge_cooc_build": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_cooc_build_rows": (C.c_int, [_P, _I32, _I32, C.POINTER(_I64), C.POINTER(_F64)]),

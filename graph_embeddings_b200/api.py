@@ -128,6 +128,9 @@ class _Native:
             raise GraphEmbError(rc, self.L.ge_last_error(self.h).decode())
         return rc
 
+    def set_stream(self, cuda_stream: int | None):
+        self.ck(self.L.ge_set_stream(self.h, C.c_void_p(cuda_stream or 0)))
+
     def close(self):
         if getattr(self, "h", None):
             self.L.ge_destroy(self.h)

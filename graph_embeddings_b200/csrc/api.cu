@@ -119,11 +119,20 @@ extern "C" int ge_create(const ge_config* cfg, ge_ctx** out) {
             return GE_ERR_NODEVICE;
         }
     }
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+    ctx->stream = ctx->own_stream;
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
     if (e != cudaSuccess) { g_create_err = cudaGetErrorString(e); delete ctx; return GE_ERR_CUDA; }
     *out = ctx;
+    return GE_OK;
+}
+
+extern "C" int ge_set_stream(ge_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return GE_ERR_INVALID;
+    cudaSetDevice(ctx->cfg.device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return GE_OK;
 }
 
@@ -136,7 +145,7 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     free_graph(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
 

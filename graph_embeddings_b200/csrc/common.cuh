@@ -65,7 +65,8 @@ struct ge_ctx {
     ge_config cfg;
     std::string err;
     int sm_count = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // stream all work is issued on (own_stream or the caller's)
+    cudaStream_t own_stream = nullptr;
 
     // --- graph (A1) ---
     int32_t V = 0;

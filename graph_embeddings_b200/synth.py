@@ -212,3 +212,51 @@ def synthetic_coo(V: int, nnz: int, seed: int = 6, s: float = 1.0):
     j = (_mix64(j.astype(np.uint64) + np.uint64(seed + 1)) % np.uint64(V)).astype(np.int32)
     x = rng.uniform(1e-4, 0.2, nnz).astype(np.float32)
     return i, j, x
+
+
+def rmat_torch(V: int, E: int, seed: int, device="cuda", a=0.57, b=0.19, c=0.19, light_frac=0.1) -> CsrGraph:
+    """Same construction as rmat() but generated with torch on `device` (bench-scale graphs:
+    100 M edges in seconds).  The random stream differs from the numpy version; parity tests
+    use rmat(), the bench only needs a graph of the configured shape."""
+    import torch
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    bits = max(1, int(np.ceil(np.log2(V))))
+    src = torch.zeros(E, dtype=torch.int64, device=device)
+    dst = torch.zeros(E, dtype=torch.int64, device=device)
+    for _ in range(bits):
+        r = torch.rand(E, device=device, generator=gen)
+        sbit = (r >= (a + b)).to(torch.int64)
+        dbit = (((r >= a) & (r < a + b)) | (r >= a + b + c)).to(torch.int64)
+        src = (src << 1) | sbit
+        dst = (dst << 1) | dbit
+    del r, sbit, dbit
+
+    def lsr(x, n):  # logical shift right on int64
+        return (x >> n) & ((1 << (64 - n)) - 1)
+
+    def mix(x):
+        x = (x ^ lsr(x, 30)) * (-4658895280553007687)   # 0xBF58476D1CE4E5B9 as int64
+        x = (x ^ lsr(x, 27)) * (-7723592293110705685)   # 0x94D049BB133111EB as int64
+        return x ^ lsr(x, 31)
+
+    salt = (seed * 0x9E3779B97F4A7C15) & 0x7FFFFFFFFFFFFFFF
+    src = lsr(mix(src ^ salt), 1) % V
+    dst = lsr(mix(dst ^ salt), 1) % V
+    keep = src != dst
+    src, dst = src[keep], dst[keep]
+    key = torch.unique((src << 32) | dst)           # sorted, duplicates removed
+    src, dst = key >> 32, key & 0xFFFFFFFF
+    h = lsr(mix(key + seed), 1) % 1000
+    w = torch.where(h < int(light_frac * 1000), 0.1, 1.0).to(torch.float32)
+    out_off = torch.zeros(V + 1, dtype=torch.int64, device=device)
+    out_off[1:] = torch.cumsum(torch.bincount(src, minlength=V), 0)
+    order = torch.argsort((dst << 32) | src)
+    in_off = torch.zeros(V + 1, dtype=torch.int64, device=device)
+    in_off[1:] = torch.cumsum(torch.bincount(dst, minlength=V), 0)
+    g = CsrGraph(V, out_off.cpu().numpy(), dst.to(torch.int32).cpu().numpy(), w.cpu().numpy(),
+                 in_off.cpu().numpy(), src[order].to(torch.int32).cpu().numpy(), w[order].cpu().numpy())
+    del key, src, dst, h, w, order
+    torch.cuda.empty_cache() if str(device).startswith("cuda") else None
+    return g

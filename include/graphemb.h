@@ -92,6 +92,10 @@ int ge_create(const ge_config* cfg, ge_ctx** out);
 void ge_destroy(ge_ctx* ctx);
 const char* ge_last_error(const ge_ctx* ctx); /* ctx may be NULL: last create error */
 const char* ge_version(void);
+/* run all device work of this handle on the caller's CUDA stream (a cudaStream_t passed as
+ * void*; NULL restores the handle's own stream) so a host that owns streams/events (e.g. a
+ * torch process timing with CUDA events) brackets exactly this library's launches */
+int ge_set_stream(ge_ctx* ctx, void* cuda_stream);
 
 /* A1 — adjacency hand-off (BookmarkColoring.java:49-52).  Neighbour lists must be sorted by
  * id and unique; off arrays have V+1 entries.  Copies to the device. */
