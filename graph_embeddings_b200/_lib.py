@@ -62,8 +62,11 @@ SIGNATURES = {
     "ge_train_stats": (C.c_int, [_P, C.POINTER(_F64), C.POINTER(_I64), C.POINTER(_I64)]),
     "ge_dist_unique_id": (C.c_int, [_P]),
     "ge_dist_init": (C.c_int, [_P, _I32, _I32, _P]),
+    "ge_dist_row_range": (C.c_int, [_P, _I32, _I32, C.POINTER(_I32), C.POINTER(_I32)]),
     "ge_dist_prepare": (C.c_int, [_P, _I32]),
     "ge_dist_train_epoch": (C.c_int, [_P, C.POINTER(_F64)]),
+    "ge_dist_extract_f32": (C.c_int, [_P, _P, _I64]),
+    "ge_dist_stats": (C.c_int, [_P, _P, _I32, C.POINTER(_F64), C.POINTER(_I64)]),
 }
 
 

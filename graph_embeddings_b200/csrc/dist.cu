@@ -1,14 +1,375 @@
-// dist.cu — multi-GPU block-rotation trainer; filled in below.
+// dist.cu — multi-GPU trainer: nb x nb block grid with ring rotation of the C blocks
+// (K7 block bucketing).  One process per GPU; the only exchange step is one
+// ncclSend/ncclRecv of a C block (rows + AdaGrad state + bias, one contiguous slab) per
+// sub-epoch, plus one all-reduce of the fp64 loss per epoch.
+//
+// Ids are cut into nb contiguous blocks of Bs = ceil(V/nb) ids.  Rank r (of p, p | nb, m = nb/p)
+// owns row-blocks r*m .. r*m+m-1: their W rows never move.  Think of nb virtual ranks; virtual
+// rank v owns row-block v and in sub-epoch s updates block (v, (v+s) mod nb).  No two virtual
+// ranks share a W or a C block within a sub-epoch, so cross-GPU updates are race-free; inside a
+// block the update kernel is the single-GPU one (Hogwild with atomic row reductions).
+// Rank r therefore needs the cyclic window of m C blocks starting at (r*m+s) mod nb; moving from
+// s to s+1 it hands the window's first block to rank r-1 and receives a new last block from
+// rank r+1.  After nb sub-epochs every C block is home again.
+//
+// Replaces the reference's thread slicing of the shuffled nonzeros (J/opt/Optimizer.java:59-63,
+// J/opt/grad/Adagrad.java:47-49), which has no multi-device counterpart.
 #include "common.cuh"
 
-struct DistState { int dummy; };
+#include <dlfcn.h>
+
+#include <cstring>
+
+namespace {
+
+// ---- NCCL through dlopen (torch already has libnccl.so.2 loaded; no link-time dependency) ----
+typedef struct ncclComm* ncclComm_t;
+struct NcclId { char internal[GE_NCCL_ID_BYTES]; };
+enum { NCCL_UINT8 = 1, NCCL_INT64 = 4, NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2 };
+struct NcclApi {
+    void* h = nullptr;
+    int (*GetUniqueId)(NcclId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, NcclId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool load(std::string& err) {
+        if (h) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+        if (!h) { err = std::string("cannot load libnccl: ") + dlerror(); return false; }
+#define SYM(f, s) f = reinterpret_cast<decltype(f)>(dlsym(h, s)); if (!f) { err = std::string("libnccl lacks ") + s; return false; }
+        SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
+        SYM(Send, "ncclSend") SYM(Recv, "ncclRecv") SYM(AllReduce, "ncclAllReduce")
+        SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd") SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+}  // namespace
+
+struct DistState {
+    int rank = 0, world = 1;
+    ncclComm_t comm = nullptr;
+    int nb = 0, m = 0;            // blocks per side, blocks per rank
+    int32_t Bs = 0;               // ids per block
+    int32_t row_base = 0, row_cnt = 0;
+    int64_t nnz_global = 0;
+    std::vector<int64_t> bucket_off;  // m*nb + 1 offsets into d_nzb, bucket = local_rowblock*nb + colblock
+    NzEntry* d_nzb = nullptr;         // bucketed nonzeros, block-local indices
+    float* d_Cring = nullptr;         // (m+1) slots x Bs rows x S floats (m slots when world == 1)
+    int head = 0;                     // slot of the window's first block
+    int sub = 0;                      // sub-epochs done in the current rotation (block ids derive from it)
+    double comm_seconds = 0;
+    cudaEvent_t c0 = nullptr, c1 = nullptr;
+};
 
 void ge_dist_free(ge_ctx* ctx) {
-    delete ctx->dist;
+    DistState* d = ctx->dist;
+    if (!d) return;
+    cudaFree(d->d_nzb);
+    cudaFree(d->d_Cring);
+    if (d->c0) cudaEventDestroy(d->c0);
+    if (d->c1) cudaEventDestroy(d->c1);
+    if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
+    delete d;
     ctx->dist = nullptr;
 }
 
-extern "C" int ge_dist_unique_id(void*) { return GE_ERR_DIST; }
-extern "C" int ge_dist_init(ge_ctx* ctx, int32_t, int32_t, const void*) { if (ctx) ctx->err = "multi-GPU path not built yet"; return GE_ERR_DIST; }
-extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t) { if (ctx) ctx->err = "multi-GPU path not built yet"; return GE_ERR_DIST; }
-extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double*) { if (ctx) ctx->err = "multi-GPU path not built yet"; return GE_ERR_DIST; }
+namespace {
+
+#define GE_NCCL(call)                                                                    \
+    do {                                                                                 \
+        int r__ = (call);                                                                \
+        if (r__ != 0) {                                                                  \
+            ctx->err = std::string(#call) + ": " + g_nccl.GetErrorString(r__);           \
+            return GE_ERR_DIST;                                                          \
+        }                                                                                \
+    } while (0)
+
+__global__ void bucket_count(const int32_t* __restrict__ I, const int32_t* __restrict__ J, int64_t nnz,
+                             int32_t row_base, int32_t Bs, int32_t nb, unsigned long long* __restrict__ cnt) {
+    __shared__ unsigned int local[1024];
+    for (int k = threadIdx.x; k < 1024; k += blockDim.x) local[k] = 0;
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const int b = ((I[k] - row_base) / Bs) * nb + J[k] / Bs;
+        atomicAdd(&local[b], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 1024; k += blockDim.x)
+        if (local[k]) atomicAdd(&cnt[k], (unsigned long long)local[k]);
+}
+
+// scatter into buckets with block-local indices; warp-aggregated cursor claims
+__global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
+                               const float* __restrict__ X, int64_t nnz, int32_t row_base, int32_t Bs, int32_t nb,
+                               int32_t method, double xmax, unsigned long long* __restrict__ cursor,
+                               NzEntry* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const int32_t i = I[k] - row_base, j = J[k];
+        const int cb = j / Bs;
+        const int b = (i / Bs) * nb + cb;
+        const float x = X[k];
+        NzEntry e;
+        e.i = i;             // W index: local to the rank's row range
+        e.j = j - cb * Bs;   // C index: local to the column block
+        if (method == GE_METHOD_GLOVE) {
+            e.a = (float)log((double)x);
+            e.b = ((double)x > xmax) ? 1.0f : (float)pow((double)x / xmax, 0.75);
+        } else {
+            e.a = (float)log((double)(x / (1.0f - x)));
+            e.b = x;
+        }
+        const unsigned long long at = atomicAdd(&cursor[b], 1ULL);
+        out[at] = e;
+    }
+}
+
+template <typename T>
+__global__ void dist_extract(const float* __restrict__ W, const float* __restrict__ C, int32_t rows, int32_t dim,
+                             int32_t S, T* __restrict__ out) {
+    const int64_t total = (int64_t)rows * dim, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
+        const int64_t r = k / dim;
+        const int32_t d = (int32_t)(k - r * dim);
+        out[k] = (T)__fdiv_rn(__fadd_rn(W[r * S + d], C[r * S + d]), 2.0f);
+    }
+}
+
+}  // namespace
+
+int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);  // train.cu
+
+extern "C" int ge_dist_unique_id(void* id128) {
+    std::string err;
+    if (!id128 || !g_nccl.load(err)) return GE_ERR_DIST;
+    NcclId id;
+    if (g_nccl.GetUniqueId(&id) != 0) return GE_ERR_DIST;
+    memcpy(id128, &id, GE_NCCL_ID_BYTES);
+    return GE_OK;
+}
+
+extern "C" int ge_dist_init(ge_ctx* ctx, int32_t rank, int32_t world, const void* id128) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world) { ctx->err = "bad rank/world"; return GE_ERR_INVALID; }
+    cudaSetDevice(ctx->cfg.device);
+    ge_dist_free(ctx);
+    DistState* d = new DistState();
+    d->rank = rank; d->world = world;
+    ctx->dist = d;
+    if (world > 1) {
+        if (!id128) { ctx->err = "ge_dist_init: unique id required for world > 1"; return GE_ERR_INVALID; }
+        if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
+        NcclId id;
+        memcpy(&id, id128, GE_NCCL_ID_BYTES);
+        GE_NCCL(g_nccl.CommInitRank(&d->comm, world, id, rank));
+    }
+    GE_CUDA(cudaEventCreate(&d->c0));
+    GE_CUDA(cudaEventCreate(&d->c1));
+    return GE_OK;
+}
+
+// rank's id range for an nb-block grid over V ids
+extern "C" int ge_dist_row_range(ge_ctx* ctx, int32_t V, int32_t nblocks, int32_t* first, int32_t* count) {
+    if (!ctx || !ctx->dist) { if (ctx) ctx->err = "ge_dist_init first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    if (nblocks < 1 || nblocks > 32 || nblocks % d->world) { ctx->err = "nblocks must be a multiple of the world size (<= 32)"; return GE_ERR_INVALID; }
+    const int32_t Bs = (V + nblocks - 1) / nblocks, m = nblocks / d->world;
+    int64_t lo = (int64_t)d->rank * m * Bs, hi = lo + (int64_t)m * Bs;
+    if (lo > V) lo = V;
+    if (hi > V) hi = V;
+    if (first) *first = (int32_t)lo;
+    if (count) *count = (int32_t)(hi - lo);
+    return GE_OK;
+}
+
+extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
+    if (!ctx || !ctx->dist) { if (ctx) ctx->err = "ge_dist_init first"; return GE_ERR_STATE; }
+    if (!ctx->have_cooc) { ctx->err = "no co-occurrence rows: build this rank's rows first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    const ge_config& c = ctx->cfg;
+    if (c.math != GE_MATH_FAST) { ctx->err = "the block-rotation trainer runs the FAST math path"; return GE_ERR_INVALID; }
+    cudaSetDevice(c.device);
+    cudaStream_t st = ctx->stream;
+    int32_t first = 0, count = 0;
+    int r = ge_dist_row_range(ctx, ctx->V, nblocks, &first, &count);
+    if (r) return r;
+    if (ctx->d_row_off && (ctx->row_first != first || ctx->row_count != count)) {
+        ctx->err = "co-occurrence rows do not match this rank's block range (use ge_dist_row_range)";
+        return GE_ERR_STATE;
+    }
+    d->nb = nblocks; d->m = nblocks / d->world;
+    d->Bs = (ctx->V + nblocks - 1) / nblocks;
+    d->row_base = first; d->row_cnt = count;
+
+    // global max (f(x) weight uses it, GloveCost.java:19) and global nnz (cost normaliser)
+    double* d_tmp = nullptr;
+    GE_CUDA(cudaMalloc(&d_tmp, 16));
+    double h2[2] = {ctx->xmax, 0};
+    long long hn = ctx->nnz;
+    if (d->world > 1) {
+        GE_CUDA(cudaMemcpyAsync(d_tmp, &h2[0], 8, cudaMemcpyHostToDevice, st));
+        GE_NCCL(g_nccl.AllReduce(d_tmp, d_tmp, 1, NCCL_FLOAT64, NCCL_MAX, d->comm, st));
+        GE_CUDA(cudaMemcpyAsync(&h2[0], d_tmp, 8, cudaMemcpyDeviceToHost, st));
+        GE_CUDA(cudaMemcpyAsync(d_tmp + 1, &hn, 8, cudaMemcpyHostToDevice, st));
+        GE_NCCL(g_nccl.AllReduce(d_tmp + 1, d_tmp + 1, 1, NCCL_INT64, NCCL_SUM, d->comm, st));
+        GE_CUDA(cudaMemcpyAsync(&hn, d_tmp + 1, 8, cudaMemcpyDeviceToHost, st));
+        GE_CUDA(cudaStreamSynchronize(st));
+    }
+    cudaFree(d_tmp);
+    ctx->xmax = h2[0];
+    d->nnz_global = hn;
+
+    // ---- K7: bucket the local nonzeros by (row-block, col-block)
+    const int nbuckets = d->m * d->nb;
+    unsigned long long* d_cnt = nullptr;
+    GE_CUDA(cudaMalloc(&d_cnt, 1024 * 8));
+    GE_CUDA(cudaMemsetAsync(d_cnt, 0, 1024 * 8, st));
+    if (ctx->nnz > 0)
+        bucket_count<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->nnz, first, d->Bs, d->nb, d_cnt);
+    std::vector<unsigned long long> hc(1024);
+    GE_CUDA(cudaMemcpyAsync(hc.data(), d_cnt, 1024 * 8, cudaMemcpyDeviceToHost, st));
+    GE_CUDA(cudaStreamSynchronize(st));
+    d->bucket_off.assign(nbuckets + 1, 0);
+    std::vector<unsigned long long> cur(1024, 0);
+    for (int b = 0; b < nbuckets; b++) { d->bucket_off[b + 1] = d->bucket_off[b] + (int64_t)hc[b]; cur[b] = (unsigned long long)d->bucket_off[b]; }
+    cudaFree(d->d_nzb); d->d_nzb = nullptr;
+    GE_CUDA(cudaMalloc(&d->d_nzb, (size_t)(ctx->nnz > 0 ? ctx->nnz : 1) * sizeof(NzEntry)));
+    GE_CUDA(cudaMemcpyAsync(d_cnt, cur.data(), 1024 * 8, cudaMemcpyHostToDevice, st));
+    if (ctx->nnz > 0)
+        bucket_scatter<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, first, d->Bs, d->nb,
+                                                         c.method, ctx->xmax, d_cnt, d->d_nzb);
+    GE_CUDA(cudaGetLastError());
+    GE_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_cnt);
+    // the COO arrays are no longer needed on the device once bucketed
+    cudaFree(ctx->d_I); cudaFree(ctx->d_J); cudaFree(ctx->d_X);
+    ctx->d_I = ctx->d_J = nullptr; ctx->d_X = nullptr;
+
+    // ---- store: W rows of this rank, ring of C block slots
+    ge_free_store(ctx);
+    ctx->D4 = (c.dim + 3) & ~3;
+    ctx->S = (2 * ctx->D4 + 2 + 7) & ~7;
+    const size_t slab = (size_t)d->Bs * ctx->S;  // floats per block
+    const int slots = d->world > 1 ? d->m + 1 : d->m;
+    GE_CUDA(cudaMalloc(&ctx->d_W, (size_t)d->m * slab * sizeof(float)));
+    cudaFree(d->d_Cring); d->d_Cring = nullptr;
+    GE_CUDA(cudaMalloc(&d->d_Cring, (size_t)slots * slab * sizeof(float)));
+    GE_CUDA(cudaMemsetAsync(ctx->d_W, 0, (size_t)d->m * slab * sizeof(float), st));
+    GE_CUDA(cudaMemsetAsync(d->d_Cring, 0, (size_t)slots * slab * sizeof(float), st));
+    r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, count, first);
+    if (r) return r;
+    if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
+    d->head = 0; d->sub = 0;
+    ctx->epoch = 0;
+    ctx->history.clear();
+    ctx->have_store = true;
+    GE_CUDA(cudaStreamSynchronize(st));
+    return GE_OK;
+}
+
+extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
+    if (!ctx || !ctx->dist || !ctx->dist->d_nzb) { if (ctx) ctx->err = "ge_dist_prepare first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    const ge_config& c = ctx->cfg;
+    cudaSetDevice(c.device);
+    cudaStream_t st = ctx->stream;
+    const size_t slab = (size_t)d->Bs * ctx->S;
+    const int slots = d->world > 1 ? d->m + 1 : d->m;
+    uint64_t ekey = (uint64_t)c.seed * 0x9E3779B97F4A7C15ULL + (uint64_t)(ctx->epoch + 1) * 0xD6E8FEB86659FD93ULL;
+    GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), st));
+    GE_CUDA(cudaEventRecord(ctx->ev0, st));
+    float comm_ms = 0;
+    for (int s = 0; s < d->nb; s++) {
+        // window of C blocks held now: block (rank*m + s + k) mod nb sits in slot (head + k) mod slots
+        for (int k = 0; k < d->m; k++) {
+            const int cb = (d->rank * d->m + s + k) % d->nb;
+            // virtual rank v = rank*m + k' processes column block (v + s) mod nb  =>  k' = k
+            const int lrb = k;
+            const int bucket = lrb * d->nb + cb;
+            const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
+            float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
+            int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
+                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st);
+            if (r) return r;
+        }
+        if (d->world > 1) {
+            // hand the window's first block to rank-1, receive a new last block from rank+1
+            const int to = (d->rank + d->world - 1) % d->world, from = (d->rank + 1) % d->world;
+            float* sendp = d->d_Cring + (size_t)d->head * slab;
+            float* recvp = d->d_Cring + (size_t)((d->head + d->m) % slots) * slab;
+            cudaEventRecord(d->c0, st);
+            GE_NCCL(g_nccl.GroupStart());
+            GE_NCCL(g_nccl.Send(sendp, slab * sizeof(float), NCCL_UINT8, to, d->comm, st));
+            GE_NCCL(g_nccl.Recv(recvp, slab * sizeof(float), NCCL_UINT8, from, d->comm, st));
+            GE_NCCL(g_nccl.GroupEnd());
+            cudaEventRecord(d->c1, st);
+            d->head = (d->head + 1) % slots;
+        } else {
+            // one GPU holds every block: rotation is a pointer shift of the window
+            d->head = (d->head + 1) % slots;
+        }
+    }
+    if (d->world == 1) d->head = (d->head + slots - (d->nb % slots)) % slots;  // nb shifts of an nb-ring: identity
+    GE_CUDA(cudaEventRecord(ctx->ev1, st));
+    double total = 0;
+    if (d->world > 1) GE_NCCL(g_nccl.AllReduce(ctx->d_cost, ctx->d_cost, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st));
+    GE_CUDA(cudaMemcpyAsync(&total, ctx->d_cost, sizeof(double), cudaMemcpyDeviceToHost, st));
+    GE_CUDA(cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->update_seconds += ms * 1e-3;
+    if (d->world > 1) { cudaEventElapsedTime(&comm_ms, d->c0, d->c1); d->comm_seconds += comm_ms * 1e-3 * d->nb; }
+    const double local = total / (double)d->nnz_global;
+    ctx->history.push_back(local);
+    ctx->epoch++;
+    if (cost) *cost = local;
+    return GE_OK;
+}
+
+// (W + C)/2 for this rank's id range; valid between epochs, when every C block is home
+extern "C" int ge_dist_extract_f32(ge_ctx* ctx, float* out, int64_t cap) {
+    if (!ctx || !ctx->dist || !ctx->have_store) { if (ctx) ctx->err = "ge_dist_prepare first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    const int32_t dim = ctx->cfg.dim;
+    if (cap < (int64_t)d->row_cnt * dim) { ctx->err = "extract capacity too small"; return GE_ERR_INVALID; }
+    cudaSetDevice(ctx->cfg.device);
+    cudaStream_t st = ctx->stream;
+    const size_t slab = (size_t)d->Bs * ctx->S;
+    const int slots = d->world > 1 ? d->m + 1 : d->m;
+    float* tmp = nullptr;
+    GE_CUDA(cudaMalloc(&tmp, (size_t)d->Bs * dim * sizeof(float)));
+    for (int k = 0; k < d->m; k++) {
+        const int64_t r0 = (int64_t)k * d->Bs;
+        int64_t rows = (int64_t)d->row_cnt - r0;
+        if (rows <= 0) break;
+        if (rows > d->Bs) rows = d->Bs;
+        const float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
+        dist_extract<float><<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_W + (size_t)k * slab, Cslot, (int32_t)rows, dim, ctx->S, tmp);
+        cudaError_t e = cudaMemcpyAsync(out + r0 * dim, tmp, (size_t)rows * dim * sizeof(float), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { cudaFree(tmp); GE_CUDA(e); }
+    }
+    cudaFree(tmp);
+    return GE_OK;
+}
+
+// per-rank bookkeeping: nnz of each (local row-block, col-block) bucket, seconds in rotation
+extern "C" int ge_dist_stats(ge_ctx* ctx, int64_t* bucket_nnz, int32_t cap, double* comm_seconds, int64_t* nnz_global) {
+    if (!ctx || !ctx->dist) return GE_ERR_STATE;
+    DistState* d = ctx->dist;
+    const int n = d->m * d->nb;
+    if (bucket_nnz) for (int b = 0; b < n && b < cap; b++) bucket_nnz[b] = d->bucket_off[b + 1] - d->bucket_off[b];
+    if (comm_seconds) *comm_seconds = d->comm_seconds;
+    if (nnz_global) *nnz_global = d->nnz_global;
+    return n;
+}

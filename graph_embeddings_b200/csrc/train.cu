@@ -400,6 +400,16 @@ void ge_free_store(ge_ctx* ctx) {
     ctx->h_perm.clear(); ctx->h_perm.shrink_to_fit();
 }
 
+// store_init on caller-provided slabs: `rows` rows whose global ids start at row0 (dist.cu)
+int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0) {
+    const ge_config& c = ctx->cfg;
+    if (rows <= 0) return GE_OK;
+    store_init<<<(rows + 127) / 128, 128, 0, ctx->stream>>>(W, C, rows, c.dim, ctx->D4, ctx->S, c.seed,
+                                                          c.init == GE_INIT_JAVA, row0);
+    GE_CUDA(cudaGetLastError());
+    return GE_OK;
+}
+
 extern "C" int ge_store_init(ge_ctx* ctx) {
     if (!ctx) return GE_ERR_INVALID;
     if (ctx->V <= 0) { ctx->err = "no vocabulary: set a graph or import a matrix first"; return GE_ERR_STATE; }

@@ -1,0 +1,83 @@
+"""One-process-per-GPU front end of the block-rotation trainer (csrc/dist.cu).  torch.distributed
+is used only to hand the NCCL unique id to the other ranks; the data path is ncclSend/ncclRecv
+inside libgraphemb.so."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .api import Configuration, _Native, _ptr
+
+
+class DistTrainer:
+    def __init__(self, config: Configuration, rank: int = 0, world: int = 1, nblocks: int = 8, id_bytes: bytes | None = None):
+        self.config, self.rank, self.world, self.nb = config, rank, world, nblocks
+        self._n = _Native(config)
+        buf = C.create_string_buffer(id_bytes, _lib.NCCL_ID_BYTES) if id_bytes else None
+        self._n.ck(self._n.L.ge_dist_init(self._n.h, rank, world, buf))
+        self.V = 0
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(_lib.NCCL_ID_BYTES)
+        rc = _lib.lib().ge_dist_unique_id(buf)
+        if rc:
+            raise _lib.GraphEmbError(rc, "ncclGetUniqueId failed (libnccl not loadable?)")
+        return buf.raw
+
+    def row_range(self, V: int):
+        f, c = C.c_int32(0), C.c_int32(0)
+        self._n.ck(self._n.L.ge_dist_row_range(self._n.h, V, self.nb, C.byref(f), C.byref(c)))
+        return f.value, c.value
+
+    def build(self, graph):
+        """replicate the CSR, build this rank's co-occurrence rows (bookmarks are independent)."""
+        n, L, g = self._n, self._n.L, graph
+        arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
+                np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
+                np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
+        n.ck(L.ge_set_graph_csr(n.h, g.V, *map(_ptr, arrs)))
+        self.V = g.V
+        first, count = self.row_range(g.V)
+        nnz, xmax = C.c_int64(0), C.c_double(0)
+        n.ck(L.ge_cooc_build_rows(n.h, first, count, C.byref(nnz), C.byref(xmax)))
+        return nnz.value, xmax.value
+
+    def import_rows(self, V, I, J, X, xmax=0.0):
+        """feed nonzeros whose rows already lie in this rank's range."""
+        I = np.ascontiguousarray(I, np.int32); J = np.ascontiguousarray(J, np.int32); X = np.ascontiguousarray(X, np.float32)
+        self._n.ck(self._n.L.ge_cooc_import(self._n.h, V, len(I), _ptr(I), _ptr(J), _ptr(X), float(xmax)))
+        self.V = V
+
+    def cooc_stats(self):
+        pops, scanned, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
+        self._n.ck(self._n.L.ge_cooc_stats(self._n.h, C.byref(pops), C.byref(scanned), C.byref(sec)))
+        return {"pops": pops.value, "scanned": scanned.value, "seconds": sec.value}
+
+    def prepare(self):
+        self._n.ck(self._n.L.ge_dist_prepare(self._n.h, self.nb))
+
+    def epoch(self) -> float:
+        cost = C.c_double(0)
+        self._n.ck(self._n.L.ge_dist_train_epoch(self._n.h, C.byref(cost)))
+        return cost.value
+
+    def extract_local(self) -> np.ndarray:
+        _, count = self.row_range(self.V)
+        out = np.empty((count, self.config.dim), np.float32)
+        self._n.ck(self._n.L.ge_dist_extract_f32(self._n.h, _ptr(out), out.size))
+        return out
+
+    def stats(self):
+        b = np.zeros(1024, np.int64)
+        comm, nnzg = C.c_double(0), C.c_int64(0)
+        n = self._n.ck(self._n.L.ge_dist_stats(self._n.h, _ptr(b), 1024, C.byref(comm), C.byref(nnzg)))
+        s, l, u = C.c_double(0), C.c_int64(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
+        return {"bucket_nnz": b[:n].copy(), "comm_seconds": comm.value, "nnz_global": nnzg.value,
+                "update_seconds": s.value, "launches": l.value, "updates": u.value}
+
+    def set_stream(self, s):
+        self._n.set_stream(s)

@@ -1,0 +1,109 @@
+"""bench.py for N > 1: one process per GPU under torchrun (RANK / LOCAL_RANK / WORLD_SIZE)."""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+
+
+def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
+    import torch
+    import torch.distributed as dist
+    from . import BCA, Configuration, Opt
+    from .dist import DistTrainer
+
+    ALPHA, EPS, SEED = consts
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    V, E, dim, desc = WORKLOADS[args.workload]
+    K, W = args.steps, args.warmup
+    g = make_graph(V, E, True)                     # same seed on every rank: replicated CSR
+    cfg = Configuration(method="glove", dim=dim, bca=BCA(ALPHA, EPS, True), opt=Opt("adagrad", 0.0, K), seed=12345,
+                        init="java", order="device", math="fast", update="atomic", device=local)
+    idb = [DistTrainer.unique_id() if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(idb, src=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- e2e from host buffers: hand-off H2D, sharded build, prepare, K epochs, result D2H
+    barrier()
+    t0 = time.time()
+    tr = DistTrainer(cfg, rank, world, 8, idb[0])
+    nnz_local, _ = tr.build(g)
+    tr.prepare()
+    for _ in range(K):
+        tr.epoch()
+    emb = tr.extract_local()
+    barrier()
+    t_e2e = time.time() - t0
+    assert np.isfinite(emb).all()
+    d2h = emb.nbytes + 8 * K
+    del emb
+    cst = tr.cooc_stats()
+    st0 = tr.stats()
+    nnz = st0["nnz_global"]
+
+    # ---- timed region: W warm-up + K epochs, CUDA events on the launching stream, max over ranks
+    tr.set_stream(torch.cuda.current_stream().cuda_stream)
+    for _ in range(W):
+        tr.epoch()
+    s0 = tr.stats()
+    clocks = ClockSampler(local).start() if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    costs = [tr.epoch() for _ in range(K)]
+    ev1.record()
+    barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
+    s1 = tr.stats()
+    stats = torch.tensor([cst["seconds"], float(cst["pops"]), float(cst["scanned"]), s1["update_seconds"] - s0["update_seconds"],
+                          s1["comm_seconds"] - s0["comm_seconds"], float(nnz_local), t_e2e], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        allst = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(allst, stats)
+    else:
+        allst = [stats]
+    clk = clocks.stop() if clocks else None
+    if rank == 0:
+        A = torch.stack(allst).cpu().numpy()
+        ms = float(ms.item())
+        peak, peak_src = peaks()
+        B = 32 * dim + 44
+        kern_s = A[:, 3].max() / K                      # slowest rank's update time per epoch (events)
+        achieved = nnz * B / kern_s / 1e9               # whole-job algorithmic GB/s
+        build_s = A[:, 0].max()
+        h2d = (g.out_off.nbytes * 2 + g.out_nbr.nbytes * 2 + g.out_w.nbytes * 2) * world
+        line = {"metric": "glove_nnz_updates_per_sec", "value": nnz * K / (ms * 1e-3), "unit": "nnz_updates/s",
+                "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": desc, "V": g.V, "E": g.E, "nnz": int(nnz), "dim": dim, "alpha": ALPHA, "epsilon": EPS,
+                           "method": "glove", "optimizer": "adagrad", "parallelism": f"8x8 block rotation over {world} GPU(s), "
+                           "NCCL send/recv of one C block per sub-epoch", "math": "f32 fast path, atomic red.add row updates",
+                           "l2": "inputs larger than L2", "final_cost": costs[-1],
+                           "nnz_per_rank": [int(x) for x in A[:, 5]],
+                           "rotation_seconds_per_epoch_max": float(A[:, 4].max() / K)},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
+                             "frac": achieved / (peak * world), "traffic": None, "kernel": "glove_adagrad_update",
+                             "bytes_per_nnz": B, "peak_source": peak_src + f" x {world} GPUs",
+                             "kernel_ms": kern_s * 1e3},
+                "cooc": {"pairs_per_s": float(A[:, 1].sum() / build_s), "nnz_per_s": float(nnz / build_s), "seconds": float(build_s),
+                         "pops": int(A[:, 1].sum()), "scanned": int(A[:, 2].sum())},
+                "e2e": {"value": nnz * K / float(A[:, 6].max()), "unit": "nnz_updates/s", "h2d_bytes_per_step": h2d / K,
+                        "d2h_bytes_per_step": d2h * world / K, "seconds": float(A[:, 6].max()),
+                        "includes": "graph hand-off H2D (replicated), sharded BCA build, bucketing, store init, K epochs "
+                                    "with loss all-reduce + read-back, f32 result D2H"},
+                "gpu_launches": int(s1["launches"] - s0["launches"]) * world, "clocks": clk}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

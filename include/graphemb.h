@@ -84,8 +84,8 @@ typedef struct ge_ctx ge_ctx;
 /* per-epoch progress (Optimizer.java:97-101): return non-zero to stop early */
 typedef int (*ge_epoch_cb)(void* user, int32_t epoch, double cost, double seconds);
 
-/* fills *cfg with the reference defaults of the shipped configs (pglove? no: glove, d=300 is
- * the caller's business) — alpha .1, eps 1e-3, directed, adagrad, tol 1e-4, maxiter 1000 */
+/* fills *cfg with the values of the shipped *.config.yml files: pglove, dim 300, alpha .1,
+ * epsilon 1e-3, directed, adagrad, tolerance 1e-4, maxiter 1000 (dblp.config.yml:2-3,17-26) */
 void ge_config_default(ge_config* cfg);
 
 int ge_create(const ge_config* cfg, ge_ctx** out);
@@ -139,14 +139,26 @@ int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);
 /* device seconds and kernel launches spent in update kernels so far */
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
 
-/* --- multi-GPU (one process per GPU) ------------------------------------ */
+/* --- multi-GPU (one process per GPU).  No reference counterpart: replaces the
+ * thread slicing of J/opt/Optimizer.java:59-63 across devices. ---------------------------- */
 #define GE_NCCL_ID_BYTES 128
-/* rank 0 creates the id, the host distributes it (torch.distributed / file / env) */
+/* rank 0 creates the id; the host distributes it (torch.distributed / file / env) */
 int ge_dist_unique_id(void* id128);
+/* world == 1 needs no id: the block schedule then runs on one GPU (rotation = pointer shift) */
 int ge_dist_init(ge_ctx*, int32_t rank, int32_t world, const void* id128);
-/* block grid: nblocks x nblocks (8 x 8 in the north star); bucket the local COO rows */
+/* this rank's id range in an nblocks x nblocks grid over V ids: build exactly these rows
+ * (ge_cooc_build_rows) or import nonzeros whose rows lie in it */
+int ge_dist_row_range(ge_ctx*, int32_t V, int32_t nblocks, int32_t* first, int32_t* count);
+/* all-reduce max()/nnz, bucket the local nonzeros by (row-block, col-block), allocate and
+ * initialise this rank's W rows and its ring of C-block slots */
 int ge_dist_prepare(ge_ctx*, int32_t nblocks);
+/* one epoch = nblocks sub-epochs, each followed by the ring rotation of one C block
+ * (ncclSend to rank-1 / ncclRecv from rank+1); cost = global localCost (all-reduced) */
 int ge_dist_train_epoch(ge_ctx*, double* cost);
+/* (W+C)/2 of this rank's id range, row-major count x dim */
+int ge_dist_extract_f32(ge_ctx*, float* out, int64_t cap);
+/* returns the number of local buckets and fills their nnz; seconds spent in rotations */
+int ge_dist_stats(ge_ctx*, int64_t* bucket_nnz, int32_t cap, double* comm_seconds, int64_t* nnz_global);
 
 #ifdef __cplusplus
 }
