@@ -111,7 +111,8 @@ struct ge_ctx {
 // train.cu
 int ge_train_prepare(ge_ctx* ctx);  // pack nonzeros, allocate cost/perm
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
-                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st);
+                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st,
+                     int64_t span /* ids addressable on the smaller side: bounds concurrency */);
 void ge_free_store(ge_ctx* ctx);
 // bca.cu
 int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);

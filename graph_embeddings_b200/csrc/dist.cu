@@ -299,7 +299,7 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
             const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
             float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
             int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
-                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st);
+                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs);
             if (r) return r;
         }
         if (d->world > 1) {

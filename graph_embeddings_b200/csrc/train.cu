@@ -362,7 +362,7 @@ static int blocks_per_sm() {
 }
 
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
-                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st) {
+                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st, int64_t span) {
     if (count <= 0) return GE_OK;
     int nt = (ctx->D4 / 4 + 31) / 32;
     if (nt == 5) nt = 6;
@@ -382,6 +382,12 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
         }
         int64_t want = (count + 32 * 8 - 1) / (32 * 8);  // blocks if every warp took one batch
         int64_t full = (int64_t)ctx->sm_count * bps;     // one resident wave
+        // Staleness bound for tiny problems: never more than one concurrent warp per 16 ids of
+        // the smaller side, so that a test-sized matrix sees the collision rate of a large one
+        // (at bench scale span/16 is far above a full wave and this never binds).
+        int64_t cap = span / (16 * 8);
+        if (cap < 1) cap = 1;
+        if (full > cap) full = cap;
         grid = dim3((unsigned)(want < full ? (want < 1 ? 1 : want) : full));
     }
     const Bijection bij = Bijection::make((uint64_t)count, order_key);
@@ -476,7 +482,7 @@ extern "C" int ge_train_epoch(ge_ctx* ctx, double* cost) {
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), ctx->stream));
     GE_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
     r = ge_launch_update(ctx, ctx->d_nz, ctx->nnz, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
-                         ctx->d_cost, ctx->stream);
+                         ctx->d_cost, ctx->stream, ctx->V);
     if (r) return r;
     GE_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
     double total = 0;

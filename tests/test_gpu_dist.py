@@ -27,11 +27,26 @@ def test_block_schedule_loss_matches_reference(method):
     expect = np.bincount((ref.I // Bs) * 8 + ref.J // Bs, minlength=64)
     assert np.array_equal(st["bucket_nnz"], expect)
     got = np.array([t.epoch() for _ in range(epochs)])
+    # (1) the reference arithmetic, single-threaded, walked in the SAME block order (sub-epoch s:
+    #     blocks (k, (k+s) mod 8), random inside a block): every epoch inside 1 %
     o = oracle.Trainer(g.V, ref.I, ref.J, ref.X, ref.max, dim, method, 31)
-    hist, _ = o.optimize(epochs, 0.0)
+    bucket = (ref.I // Bs) * 8 + ref.J // Bs
+    rng = np.random.default_rng(1)
+    hb = []
+    for _ in range(epochs):
+        order = [rng.permutation(np.nonzero(bucket == k * 8 + (k + s) % 8)[0]) for s in range(8) for k in range(8)]
+        o.set_perm(np.concatenate(order).astype(np.int32))
+        hb.append(o.epoch(False))
+    relb = np.abs(got - np.array(hb)) / np.array(hb)
+    assert relb.max() < 0.01, relb
+    # (2) the reference in its own (globally shuffled) order: the block schedule visits the heavy
+    #     diagonal entries X_ii first, which shifts the first epochs' *online* loss for ANY
+    #     implementation of this schedule; from the 5th epoch on it is inside 1 %
+    o2 = oracle.Trainer(g.V, ref.I, ref.J, ref.X, ref.max, dim, method, 31)
+    hist, _ = o2.optimize(epochs, 0.0)
     rel = np.abs(got - hist) / hist
-    assert rel.max() < 0.01, rel
+    assert rel[4:].max() < 0.01, rel
     emb = t.extract_local()
     assert emb.shape == (g.V, dim) and np.isfinite(emb).all()
-    # store initialisation is the reference stream regardless of blocking: epoch-0 cost agrees tightly
-    assert rel[0] < 2e-3
+    a, b = emb.astype(np.float64).ravel(), o.extract().ravel()
+    assert a @ b / (np.linalg.norm(a) * np.linalg.norm(b)) > 0.9      # same solution up to SGD noise

@@ -107,7 +107,15 @@ def test_fast_hogwild_loss_within_1pct_and_nn_overlap(method):
     hist, _ = t.optimize(epochs, 0.0)
     got = np.array(opt.costHistory)
     rel = np.abs(got - hist) / hist
-    assert len(got) == epochs and rel.max() < 0.01, rel
+    # device epoch order: the first epoch carries shuffle noise of its own (the reference against
+    # itself under another shuffle differs by ~0.8 % there), later epochs must be inside 1 %
+    assert len(got) == epochs and rel[0] < 0.02 and rel[1:].max() < 0.01, rel
+    # same epoch order as the reference (host Fisher-Yates replay), thousands of Hogwild warps:
+    # every epoch inside 1 %
+    cj = cfg(method=method, dim=dim, maxiter=epochs, seed=31, order="java")
+    gotj = np.array(createOptimizer(cj, ImportedMatrix(g.V, I, J, X, cj, xmax=bca.max())).optimize().costHistory)
+    relj = np.abs(gotj - hist) / hist
+    assert relj.max() < 0.01, relj
     # reference vs itself under another epoch order (same init, same arithmetic, 1 thread)
     t2 = oracle.Trainer(g.V, I, J, X, bca.max(), dim, method, 31)
     rng = np.random.default_rng(5)
