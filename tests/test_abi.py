@@ -1,0 +1,74 @@
+"""CPU-side checks of the drop-in boundary: libgraphemb.so loads and exports every symbol that
+include/graphemb.h declares; no compute call is made (there is no GPU here and no fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from graph_embeddings_b200 import _lib
+from graph_embeddings_b200.api import BCA, Configuration, InvalidConfigurationException, Opt
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "graphemb.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ge_[a-z0-9_]+)\s*\(", src)) - {"ge_epoch_cb"})
+
+
+def test_library_exports_every_declared_symbol():
+    _lib.build()
+    L = C.CDLL(_lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/graphemb.h but not exported"
+    assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
+
+
+def test_version_and_default_config_need_no_device():
+    L = _lib.lib()
+    assert b"sm_100a" in L.ge_version()
+    c = _lib.GeConfig()
+    L.ge_config_default(C.byref(c))
+    # the shipped *.config.yml values (dblp.config.yml:2-3,17-26) and Optimizer.java:26
+    assert (c.dim, c.method, c.directed, c.maxiter) == (300, _lib.METHOD["pglove"], 1, 1000)
+    assert (c.alpha, c.epsilon, c.tolerance) == (0.1, 1e-3, 1e-4)
+    assert abs(c.learning_rate - 0.05) < 1e-9
+
+
+def test_config_struct_layout_matches_header():
+    # field order of ge_config in the header == ctypes mirror
+    src = open(os.path.join(ROOT, "include", "graphemb.h")).read()
+    body = src[src.index("typedef struct ge_config {"):src.index("} ge_config;")]
+    fields = re.findall(r"^\s*(?:int32_t|int64_t|double|float)\s+([a-z_]+);", body, flags=re.M)
+    assert fields == [f[0] for f in _lib.GeConfig._fields_]
+
+
+def test_create_fails_loudly_without_gpu_or_with_bad_config():
+    import torch
+    L = _lib.lib()
+    c = _lib.GeConfig()
+    L.ge_config_default(C.byref(c))
+    h = C.c_void_p()
+    c.dim = 0
+    assert L.ge_create(C.byref(c), C.byref(h)) == -1 and b"dimension" in L.ge_last_error(None)
+    c.dim, c.alpha = 8, 0.0
+    assert L.ge_create(C.byref(c), C.byref(h)) == -1 and b"alpha and epsilon" in L.ge_last_error(None)
+    c.alpha = 0.1
+    if not torch.cuda.is_available():
+        assert L.ge_create(C.byref(c), C.byref(h)) == -7          # GE_ERR_NODEVICE: no CPU fallback
+        assert b"no CPU fallback" in L.ge_last_error(None)
+
+
+def test_configuration_check_mirrors_reference_messages():
+    ok = Configuration(graph="g.ttl", method="glove", dim=8, bca=BCA(0.1, 1e-3, True), opt=Opt(), output={"uri": []})
+    Configuration.check(ok)
+    for mut, msg in [(dict(dim=0), "No dimension specified"), (dict(graph=None), "No input graph specified"),
+                     (dict(method=None), "Invalid method"), (dict(bca=BCA(0.0, 1e-3)), "alpha and epsilon are mandatory"),
+                     (dict(output=None), "specify at least one group")]:
+        bad = Configuration(**{**ok.__dict__, **mut})
+        with pytest.raises(InvalidConfigurationException, match=msg):
+            Configuration.check(bad)
