@@ -13,7 +13,7 @@ GE_OK = 0
 ERRORS = {-1: "GE_ERR_INVALID", -2: "GE_ERR_STATE", -3: "GE_ERR_CUDA", -4: "GE_ERR_NOMEM",
           -5: "GE_ERR_GRAPH", -6: "GE_ERR_DIST", -7: "GE_ERR_NODEVICE"}
 METHOD = {"glove": 0, "pglove": 1}
-OPT = {"adagrad": 0}
+OPT = {"adagrad": 0, "adam": 1, "amsgrad": 2}
 NORM = {"none": 0, "unity": 1, "counts": 2}
 MATH = {"fast": 0, "java": 1}
 ORDER = {"device": 0, "java": 1}

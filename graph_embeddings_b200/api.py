@@ -90,7 +90,7 @@ class Configuration:
             raise ValueError("Invalid cost function")             # Main.java:111-112
         om = (self.opt.method if self.opt else "adagrad").lower()
         if om not in _lib.OPT:
-            raise ValueError("Invalid optimization method")        # Main.java:122-123 (adagrad only here)
+            raise ValueError("Invalid optimization method")        # Main.java:122-123
         c = GeConfig()
         _lib.lib().ge_config_default(C.byref(c))
         c.dim, c.method, c.opt_method = self.dim, _lib.METHOD[m], _lib.OPT[om]
@@ -164,6 +164,7 @@ class BookmarkColoring(CoOccurrenceMatrix):
 
     def __init__(self, graph, config: Configuration, keys=None, types=None, rows=None):
         Configuration.check(config, require_io=False)
+        self.config = config
         self._n = _Native(config)
         n, L = self._n, self._n.L
         g = graph
@@ -223,6 +224,7 @@ class ImportedMatrix(BookmarkColoring):
 
     def __init__(self, V, I, J, X, config: Configuration, xmax: float = 0.0):
         Configuration.check(config, require_io=False)
+        self.config = config
         self._n = _Native(config)
         I = np.ascontiguousarray(I, np.int32); J = np.ascontiguousarray(J, np.int32); X = np.ascontiguousarray(X, np.float32)
         self._n.ck(self._n.L.ge_cooc_import(self._n.h, V, len(I), _ptr(I), _ptr(J), _ptr(X), float(xmax)))
@@ -303,7 +305,7 @@ class Adagrad(IOptimizer):
 
     def store(self, name) -> np.ndarray:
         which = {"focus": 0, "context": 1, "fBias": 2, "cBias": 3, "gsFocus": 4, "gsContext": 5,
-                 "gsFBias": 6, "gsCBias": 7}[name]
+                 "gsFBias": 6, "gsCBias": 7, "m1Focus": 8, "m1Context": 9, "m1FBias": 10, "m1CBias": 11}[name]
         V, d = self.coMatrix.vocabSize(), self.config.dim
         out = np.empty((V,) if (which >> 1) & 1 else (V, d), np.float32)
         self._n.ck(self._n.L.ge_store_export(self._n.h, which, _ptr(out)))
@@ -320,10 +322,27 @@ class Adagrad(IOptimizer):
         return {"update_seconds": s.value, "launches": l.value, "updates": u.value}
 
 
+class Adam(Adagrad):
+    """new Adam(coMatrix, config, costFunction) (J/opt/grad/Adam.java:55-66); same epoch loop
+    (Optimizer.optimize), update kernel = adam_update.  store("gs*") are the second moments."""
+
+    def getName(self): return "Adam"
+
+
+class AMSGrad(Adagrad):
+    """new AMSGrad(coMatrix, config, costFunction) (J/opt/grad/AMSGrad.java:72-83)."""
+
+    def getName(self): return "AMSGrad"
+
+
 def createOptimizer(config: Configuration, coMatrix: BookmarkColoring, on_epoch=None) -> IOptimizer:
-    """Main.createOptimizer (J/Main.java:107-131)."""
+    """Main.createOptimizer (J/Main.java:107-131).  The matrix handle was created with
+    config.opt.method, which fixes the store layout; the class only names it."""
     if (config.method or "").lower() not in ("glove", "pglove"):
         raise ValueError("Invalid cost function")
-    if (config.opt.method if config.opt else "adagrad").lower() != "adagrad":
+    om = (config.opt.method if config.opt else "adagrad").lower()
+    if om not in _lib.OPT:
         raise ValueError("Invalid optimization method")
-    return Adagrad(coMatrix, config, on_epoch)
+    if coMatrix.config is not config and (coMatrix.config.opt.method if coMatrix.config.opt else "adagrad").lower() != om:
+        raise ValueError("the matrix was built for a different opt.method")
+    return {"adagrad": Adagrad, "adam": Adam, "amsgrad": AMSGrad}[om](coMatrix, config, on_epoch)

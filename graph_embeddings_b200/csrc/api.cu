@@ -97,7 +97,8 @@ extern "C" int ge_create(const ge_config* cfg, ge_ctx** out) {
     if (cfg->dim <= 0 || cfg->dim > 1024) { g_create_err = "Invalid configuration: No dimension specified (1..1024)"; return GE_ERR_INVALID; }
     if (cfg->method != GE_METHOD_GLOVE && cfg->method != GE_METHOD_PGLOVE) { g_create_err = "Invalid configuration: Invalid method, choose one of: glove, pglove"; return GE_ERR_INVALID; }
     if (!(cfg->alpha > 0) || !(cfg->epsilon > 0)) { g_create_err = "Invalid configuration: Invalid BCA parameters, alpha and epsilon are mandatory"; return GE_ERR_INVALID; }
-    if (cfg->opt_method != GE_OPT_ADAGRAD) { g_create_err = "Invalid optimization method (this build: adagrad)"; return GE_ERR_INVALID; }
+    if (cfg->opt_method < GE_OPT_ADAGRAD || cfg->opt_method > GE_OPT_AMSGRAD) { g_create_err = "Invalid optimization method"; return GE_ERR_INVALID; }
+    if (cfg->opt_method != GE_OPT_ADAGRAD && cfg->dim > 512) { g_create_err = "adam / amsgrad: dim must be <= 512"; return GE_ERR_INVALID; }
     if (cfg->normalize < 0 || cfg->normalize > 2) { g_create_err = "Invalid bca.normalize"; return GE_ERR_INVALID; }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {

@@ -91,7 +91,7 @@ struct ge_ctx {
 
     // --- embedding store (B1): two arrays of V rows x S floats,
     //     row = [vec(D4) | gradsq(D4) | bias | gradsq_bias | pad], S = roundup(2*D4+2, 8) ---
-    int32_t D4 = 0, S = 0;
+    int32_t D4 = 0, S = 0, NS = 1, BO = 0;  // NS state vectors per row, BO = offset of the bias block
     float *d_W = nullptr, *d_C = nullptr;
     bool have_store = false;
     NzEntry* d_nz = nullptr;      // packed nonzeros
@@ -114,6 +114,8 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                      const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st,
                      int64_t span /* ids addressable on the smaller side: bounds concurrency */);
 void ge_free_store(ge_ctx* ctx);
+void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
+int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
 // bca.cu
 int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);
 void ge_free_cooc(ge_ctx* ctx);

@@ -147,7 +147,6 @@ __global__ void dist_extract(const float* __restrict__ W, const float* __restric
 
 }  // namespace
 
-int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);  // train.cu
 
 extern "C" int ge_dist_unique_id(void* id128) {
     std::string err;
@@ -257,8 +256,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
 
     // ---- store: W rows of this rank, ring of C block slots
     ge_free_store(ctx);
-    ctx->D4 = (c.dim + 3) & ~3;
-    ctx->S = (2 * ctx->D4 + 2 + 7) & ~7;
+    ge_store_geometry(ctx);
     const size_t slab = (size_t)d->Bs * ctx->S;  // floats per block
     const int slots = d->world > 1 ? d->m + 1 : d->m;
     GE_CUDA(cudaMalloc(&ctx->d_W, (size_t)d->m * slab * sizeof(float)));

@@ -229,6 +229,173 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
 }
 
 // ------------------------------------------------------------------------------------------
+// Adam / AMSGrad update: J/opt/grad/Adam.java:75-146, AMSGrad.java:91-162.
+// Same gather skeleton as K6; row = [vec | M1 | M2 | bias, M1b, M2b].  Algorithmic bytes per
+// nonzero: 48*dim + 60 (6 rows each way + 6 bias scalars each way + the triple).
+// AMS: second moment = max(old, new) (AMSGrad.java:129-130), no bias correction, step
+// lr / (sqrt(v)+eps) * m (:133); Adam: step corr * m / (sqrt(v)+eps) (:118) with the per-epoch
+// `corr` of Adam.java:84 computed on the host in fp64.
+// FAST: f32 arithmetic; the parameter delta is applied with red.add (never lost), the moments
+// with plain stores (they are decayed averages, not sums: a lost write loses one sample, as in
+// the reference's own unsynchronised threads).  JAVA: the reference's promotion pattern.
+// ------------------------------------------------------------------------------------------
+template <int NT, bool JAVA, bool AMS>
+__global__ void __launch_bounds__(256)
+adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W, float* __restrict__ C,
+            const int32_t* __restrict__ perm, Bijection bij, int32_t D4, int32_t S, int32_t method,
+            double xmax, float lr, double corr_d, double* __restrict__ cost_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int nchunk = D4 >> 2;
+    const int32_t BO = 3 * D4;
+    const float b1 = 0.9f, b2 = 0.999f, epsf = 1e-7f;               // Adam.java:45-53
+    const float omb1 = __fsub_rn(1.0f, b1), omb2 = __fsub_rn(1.0f, b2);
+    const double lr_d = (double)lr, eps_d = (double)epsf;
+    const float stepf = AMS ? lr : (float)corr_d;
+    double cost_d = 0.0;
+    float cost_f = 0.0f;
+
+    for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
+        NzEntry mine = {0, 0, 0.f, 0.f};
+        const int64_t pos = base + lane;
+        if (pos < count) {
+            const int64_t idx = perm ? (int64_t)perm[pos] : (int64_t)bij((uint64_t)pos);
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(nz + idx));
+            mine.i = raw.x; mine.j = raw.y; mine.a = __int_as_float(raw.z); mine.b = __int_as_float(raw.w);
+        }
+        const int nvalid = (int)min((int64_t)32, count - base);
+        for (int t = 0; t < nvalid; t++) {
+            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
+            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
+            const float ea = __shfl_sync(0xffffffffu, mine.a, t);
+            const float eb = __shfl_sync(0xffffffffu, mine.b, t);
+            float* wrow = W + (size_t)bi * S;
+            float* crow = C + (size_t)bj * S;
+
+            float4 w[NT], c[NT], mw[NT], mc[NT], vw[NT], vc[NT];
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                const int ch = lane + 32 * q;
+                if (ch < nchunk) {
+                    w[q] = ldcg4(wrow + 4 * ch);
+                    c[q] = ldcg4(crow + 4 * ch);
+                    mw[q] = ldcg4(wrow + D4 + 4 * ch);
+                    mc[q] = ldcg4(crow + D4 + 4 * ch);
+                    vw[q] = ldcg4(wrow + 2 * D4 + 4 * ch);
+                    vc[q] = ldcg4(crow + 2 * D4 + 4 * ch);
+                } else {
+                    w[q] = c[q] = mw[q] = mc[q] = vw[q] = vc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            // bias block: (bias, M1b, M2b, pad) — 16-B aligned because BO = 3*D4 and S % 4 == 0
+            float4 bw = ldcg4(wrow + BO), bc = ldcg4(crow + BO);
+
+            float dot = 0.f;
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                if (JAVA) {
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].x, c[q].x));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].y, c[q].y));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].z, c[q].z));
+                    dot = __fadd_rn(dot, __fmul_rn(w[q].w, c[q].w));
+                } else {
+                    dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
+                }
+            }
+            dot = warp_sum(dot);
+
+            float inner, wc;
+            if (JAVA) {
+                const float x = ea;
+                double target;
+                if (method == GE_METHOD_GLOVE) target = log((double)x);
+                else target = log((double)__fdiv_rn(x, __fsub_rn(1.0f, x)));
+                inner = (float)__dadd_rn((double)dot, __dsub_rn((double)__fadd_rn(bw.x, bc.x), target));
+                if (method == GE_METHOD_GLOVE)
+                    wc = ((double)x > xmax) ? inner : __fmul_rn((float)pow(__ddiv_rn((double)x, xmax), 0.75), inner);
+                else
+                    wc = __fmul_rn(x, inner);
+                cost_f = (float)__dadd_rn((double)cost_f, __dmul_rn(__dmul_rn(0.5, (double)wc), (double)inner));
+            } else {
+                inner = dot + (bw.x + bc.x) - ea;
+                wc = eb * inner;
+                cost_d += 0.5 * (double)wc * (double)inner;
+            }
+
+            // one scalar step; returns the new parameter (JAVA) or its delta (FAST)
+            auto upd = [&](float p, float g, float& m, float& v) -> float {
+                if (JAVA) {
+                    const float m1 = __fadd_rn(__fmul_rn(b1, m), __fmul_rn(omb1, g));
+                    float v1 = __fadd_rn(__fmul_rn(b2, v), __fmul_rn(omb2, __fmul_rn(g, g)));
+                    if (AMS) v1 = (v <= v1) ? v1 : v;  // FastMath.max(old, new)
+                    m = m1; v = v1;
+                    const double den = __dadd_rn(__dsqrt_rn((double)v1), eps_d);
+                    if (AMS) return (float)__dsub_rn((double)p, __dmul_rn(__ddiv_rn(lr_d, den), (double)m1));
+                    return (float)__dsub_rn((double)p, __ddiv_rn(__dmul_rn(corr_d, (double)m1), den));
+                } else {
+                    const float m1 = b1 * m + omb1 * g;
+                    float v1 = b2 * v + omb2 * (g * g);
+                    if (AMS) v1 = fmaxf(v, v1);
+                    m = m1; v = v1;
+                    return -stepf * m1 / (sqrtf(v1) + epsf);
+                }
+            };
+
+#pragma unroll
+            for (int q = 0; q < NT; q++) {
+                const int ch = lane + 32 * q;
+                if (ch < nchunk) {
+                    float* wv = reinterpret_cast<float*>(&w[q]);
+                    float* cv = reinterpret_cast<float*>(&c[q]);
+                    float* mwv = reinterpret_cast<float*>(&mw[q]);
+                    float* mcv = reinterpret_cast<float*>(&mc[q]);
+                    float* vwv = reinterpret_cast<float*>(&vw[q]);
+                    float* vcv = reinterpret_cast<float*>(&vc[q]);
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const float gu = JAVA ? __fmul_rn(wc, cv[e]) : wc * cv[e];   // pre-update values
+                        const float gv = JAVA ? __fmul_rn(wc, wv[e]) : wc * wv[e];
+                        wv[e] = upd(wv[e], gu, mwv[e], vwv[e]);
+                        cv[e] = upd(cv[e], gv, mcv[e], vcv[e]);
+                    }
+                    if (JAVA) {
+                        st4(wrow + 4 * ch, w[q]);
+                        st4(crow + 4 * ch, c[q]);
+                    } else {
+                        red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
+                        red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
+                    }
+                    st4(wrow + D4 + 4 * ch, mw[q]);
+                    st4(crow + D4 + 4 * ch, mc[q]);
+                    st4(wrow + 2 * D4 + 4 * ch, vw[q]);
+                    st4(crow + 2 * D4 + 4 * ch, vc[q]);
+                }
+            }
+            if (lane == 0) {  // Adam.java:128-143 / AMSGrad.java:144-159 — biases: gradient = weightedCost
+                const float nbw = upd(bw.x, wc, bw.y, bw.z);
+                const float nbc = upd(bc.x, wc, bc.y, bc.z);
+                if (JAVA) {
+                    bw.x = nbw; bc.x = nbc;
+                    st4(wrow + BO, bw);
+                    st4(crow + BO, bc);
+                } else {
+                    atomicAdd(wrow + BO, nbw);  // result unused -> RED.ADD.F32: delta on the bias
+                    atomicAdd(crow + BO, nbc);
+                    wrow[BO + 1] = bw.y; wrow[BO + 2] = bw.z;
+                    crow[BO + 1] = bc.y; crow[BO + 2] = bc.z;
+                }
+            }
+            if (JAVA) __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        const double cst = JAVA ? (double)cost_f : cost_d;
+        if (cst != 0.0) atomicAdd(cost_out, cst);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // pack: (I, J, X) -> NzEntry.  FAST math folds log / pow (per-nonzero constants) into the
 // entry once, in fp64, so the hot loop has no transcendental (GloveCost.java:13,19).
 // ------------------------------------------------------------------------------------------
@@ -264,7 +431,8 @@ __device__ __forceinline__ uint32_t counter24(uint64_t seed, uint64_t idx) {
 }
 
 __global__ void store_init(float* __restrict__ W, float* __restrict__ C, int32_t V, int32_t dim,
-                           int32_t D4, int32_t S, int64_t seed, int32_t java, int32_t row0) {
+                           int32_t D4, int32_t S, int64_t seed, int32_t java, int32_t row0,
+                           int32_t NS, float g0) {
     const int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= V) return;
     const uint64_t per_row = 2 + 2 * (uint64_t)dim;
@@ -280,16 +448,18 @@ __global__ void store_init(float* __restrict__ W, float* __restrict__ C, int32_t
     };
     float* w = W + (size_t)r * S;
     float* c = C + (size_t)r * S;
-    w[2 * D4] = draw(); w[2 * D4 + 1] = 1.0f;
-    c[2 * D4] = draw(); c[2 * D4 + 1] = 1.0f;
+    const int32_t BO = (1 + NS) * D4;  // bias block: [bias | state scalars(NS)]
+    w[BO] = draw();
+    c[BO] = draw();
+    for (int s = 1; s <= NS; s++) { w[BO + s] = g0; c[BO + s] = g0; }
     for (int d = 0; d < dim; d++) {
         w[d] = draw();
         c[d] = draw();
-        w[D4 + d] = 1.0f;
-        c[D4 + d] = 1.0f;
     }
-    for (int d = dim; d < D4; d++) { w[d] = c[d] = 0.f; w[D4 + d] = c[D4 + d] = 1.0f; }
-    for (int d = 2 * D4 + 2; d < S; d++) { w[d] = 0.f; c[d] = 0.f; }
+    for (int d = dim; d < D4; d++) w[d] = c[d] = 0.f;
+    // state vectors: AdaGrad gradsq = 1 (Adagrad.java:27-33); Adam/AMSGrad moments = 0 (`new float[]`)
+    for (int d = D4; d < BO; d++) { w[d] = g0; c[d] = g0; }
+    for (int d = BO + 1 + NS; d < S; d++) { w[d] = 0.f; c[d] = 0.f; }
 }
 
 // K8 — extractResult (Optimizer.java:130-140): (focus + context) / 2 in f32, widened
@@ -354,11 +524,49 @@ static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStre
     return GE_OK;
 }
 
-template <int NT, bool JAVA>
-static int blocks_per_sm() {
-    int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, glove_adagrad_update<NT, JAVA, !JAVA>, 256, 0);
-    return n < 1 ? 1 : n;
+// grid for one resident wave of kernel `k`, bounded for tiny problems (see below)
+template <typename K>
+static dim3 wave_grid(ge_ctx* ctx, K k, int64_t count, int64_t span) {
+    int bps = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k, 256, 0);
+    if (bps < 1) bps = 1;
+    int64_t want = (count + 32 * 8 - 1) / (32 * 8);  // blocks if every warp took one batch
+    int64_t full = (int64_t)ctx->sm_count * bps;     // one resident wave
+    // Staleness bound for tiny problems: never more than one concurrent warp per 16 ids of
+    // the smaller side, so that a test-sized matrix sees the collision rate of a large one
+    // (at bench scale span/16 is far above a full wave and this never binds).
+    int64_t cap = span / (16 * 8);
+    if (cap < 1) cap = 1;
+    if (full > cap) full = cap;
+    return dim3((unsigned)(want < full ? (want < 1 ? 1 : want) : full));
+}
+
+template <bool JAVA, bool AMS>
+static int launch_adam_nt(ge_ctx* ctx, int nt, cudaStream_t st, const NzEntry* nz, int64_t count, float* W,
+                          float* C, const int32_t* perm, Bijection bij, double* d_cost, int64_t span) {
+    const ge_config& c = ctx->cfg;
+    // Adam.java:84 — learningRate * sqrt(1 - beta2^(it+1)) / (1 - beta1^(it+1)), fp64, float betas widened
+    const double it1 = (double)(ctx->epoch + 1);
+    const double corr = (double)c.learning_rate * sqrt(1 - pow((double)0.999f, it1)) / (1 - pow((double)0.9f, it1));
+#define GE_LAUNCH(NT_)                                                                             \
+    {                                                                                              \
+        auto k = adam_update<NT_, JAVA, AMS>;                                                      \
+        dim3 block(256), grid;                                                                     \
+        if (c.serial) { block = dim3(32); grid = dim3(1); }                                        \
+        else grid = wave_grid(ctx, k, count, span);                                                \
+        k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax, \
+                                  c.learning_rate, corr, d_cost);                                  \
+    }
+    switch (nt) {
+        case 1: GE_LAUNCH(1); break;
+        case 2: GE_LAUNCH(2); break;
+        case 3: GE_LAUNCH(3); break;
+        case 4: GE_LAUNCH(4); break;
+        default: ctx->err = "adam / amsgrad: dim too large (max 512)"; return GE_ERR_INVALID;
+    }
+#undef GE_LAUNCH
+    GE_CUDA(cudaGetLastError());
+    return GE_OK;
 }
 
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
@@ -368,31 +576,28 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
     if (nt == 5) nt = 6;
     if (nt == 7) nt = 8;
     const bool java = ctx->cfg.math == GE_MATH_JAVA;
-    dim3 block(256), grid;
-    if (ctx->cfg.serial) { block = dim3(32); grid = dim3(1); }
-    else {
-        int bps;
-        switch (nt) {
-            case 1: bps = java ? blocks_per_sm<1, true>() : blocks_per_sm<1, false>(); break;
-            case 2: bps = java ? blocks_per_sm<2, true>() : blocks_per_sm<2, false>(); break;
-            case 3: bps = java ? blocks_per_sm<3, true>() : blocks_per_sm<3, false>(); break;
-            case 4: bps = java ? blocks_per_sm<4, true>() : blocks_per_sm<4, false>(); break;
-            case 6: bps = java ? blocks_per_sm<6, true>() : blocks_per_sm<6, false>(); break;
-            default: bps = java ? blocks_per_sm<8, true>() : blocks_per_sm<8, false>(); break;
-        }
-        int64_t want = (count + 32 * 8 - 1) / (32 * 8);  // blocks if every warp took one batch
-        int64_t full = (int64_t)ctx->sm_count * bps;     // one resident wave
-        // Staleness bound for tiny problems: never more than one concurrent warp per 16 ids of
-        // the smaller side, so that a test-sized matrix sees the collision rate of a large one
-        // (at bench scale span/16 is far above a full wave and this never binds).
-        int64_t cap = span / (16 * 8);
-        if (cap < 1) cap = 1;
-        if (full > cap) full = cap;
-        grid = dim3((unsigned)(want < full ? (want < 1 ? 1 : want) : full));
-    }
     const Bijection bij = Bijection::make((uint64_t)count, order_key);
     ctx->launches++;
     ctx->updates += count;
+    if (ctx->cfg.opt_method != GE_OPT_ADAGRAD) {
+        const bool ams = ctx->cfg.opt_method == GE_OPT_AMSGRAD;
+        if (java) return ams ? launch_adam_nt<true, true>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span)
+                             : launch_adam_nt<true, false>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span);
+        return ams ? launch_adam_nt<false, true>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span)
+                   : launch_adam_nt<false, false>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span);
+    }
+    dim3 block(256), grid;
+    if (ctx->cfg.serial) { block = dim3(32); grid = dim3(1); }
+    else {
+        switch (nt) {
+#define GE_GRID(NT_) case NT_: grid = java ? wave_grid(ctx, glove_adagrad_update<NT_, true, false>, count, span) \
+                                          : wave_grid(ctx, glove_adagrad_update<NT_, false, true>, count, span); break;
+            GE_GRID(1) GE_GRID(2) GE_GRID(3) GE_GRID(4) GE_GRID(6)
+            default: grid = java ? wave_grid(ctx, glove_adagrad_update<8, true, false>, count, span)
+                                 : wave_grid(ctx, glove_adagrad_update<8, false, true>, count, span); break;
+#undef GE_GRID
+        }
+    }
     if (java) return launch_update_nt<true, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
     if (ctx->cfg.update == GE_UPDATE_STORE)
         return launch_update_nt<false, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
@@ -406,12 +611,22 @@ void ge_free_store(ge_ctx* ctx) {
     ctx->h_perm.clear(); ctx->h_perm.shrink_to_fit();
 }
 
+// Row geometry: [vec(D4) | NS state vectors(D4 each) | bias | NS state scalars | pad to 8 floats].
+// AdaGrad NS = 1 (gradsq); Adam / AMSGrad NS = 2 (first moment, second moment).
+void ge_store_geometry(ge_ctx* ctx) {
+    ctx->D4 = (ctx->cfg.dim + 3) & ~3;
+    ctx->NS = ctx->cfg.opt_method == GE_OPT_ADAGRAD ? 1 : 2;
+    ctx->BO = (1 + ctx->NS) * ctx->D4;
+    ctx->S = (ctx->BO + 1 + ctx->NS + 7) & ~7;
+}
+
 // store_init on caller-provided slabs: `rows` rows whose global ids start at row0 (dist.cu)
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0) {
     const ge_config& c = ctx->cfg;
     if (rows <= 0) return GE_OK;
     store_init<<<(rows + 127) / 128, 128, 0, ctx->stream>>>(W, C, rows, c.dim, ctx->D4, ctx->S, c.seed,
-                                                          c.init == GE_INIT_JAVA, row0);
+                                                          c.init == GE_INIT_JAVA, row0, ctx->NS,
+                                                          c.opt_method == GE_OPT_ADAGRAD ? 1.0f : 0.0f);
     GE_CUDA(cudaGetLastError());
     return GE_OK;
 }
@@ -421,14 +636,12 @@ extern "C" int ge_store_init(ge_ctx* ctx) {
     if (ctx->V <= 0) { ctx->err = "no vocabulary: set a graph or import a matrix first"; return GE_ERR_STATE; }
     const ge_config& c = ctx->cfg;
     cudaFree(ctx->d_W); cudaFree(ctx->d_C); ctx->d_W = ctx->d_C = nullptr;
-    ctx->D4 = (c.dim + 3) & ~3;
-    ctx->S = (2 * ctx->D4 + 2 + 7) & ~7;
+    ge_store_geometry(ctx);
     const size_t bytes = (size_t)ctx->V * ctx->S * sizeof(float);
     GE_CUDA(cudaMalloc(&ctx->d_W, bytes));
     GE_CUDA(cudaMalloc(&ctx->d_C, bytes));
-    store_init<<<(ctx->V + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, ctx->V, c.dim, ctx->D4,
-                                                             ctx->S, c.seed, c.init == GE_INIT_JAVA, 0);
-    GE_CUDA(cudaGetLastError());
+    int ri = ge_store_init_rows(ctx, ctx->d_W, ctx->d_C, ctx->V, 0);
+    if (ri) return ri;
     // stream position after the init draws: the epoch shuffles continue on the same stream
     // (Optimizer.random and Permutation.random are one thread-local instance)
     ctx->rng = JavaLcg::seeded(c.seed);
@@ -544,17 +757,20 @@ extern "C" int ge_extract(ge_ctx* ctx, double* out) { return extract_impl<double
 extern "C" int ge_extract_f32(ge_ctx* ctx, float* out) { return extract_impl<float>(ctx, out); }
 
 extern "C" int ge_store_export(ge_ctx* ctx, int32_t which, float* out) {
-    if (!ctx || !out || which < 0 || which > 7) return GE_ERR_INVALID;
+    if (!ctx || !out || which < 0 || which > 11) return GE_ERR_INVALID;
     if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
-    const int32_t dim = ctx->cfg.dim, D4 = ctx->D4;
+    const int32_t dim = ctx->cfg.dim, D4 = ctx->D4, BO = ctx->BO, NS = ctx->NS;
     const float* A = (which & 1) ? ctx->d_C : ctx->d_W;
     int32_t off, width;
     switch (which >> 1) {
-        case 0: off = 0; width = dim; break;            // focus / context
-        case 1: off = 2 * D4; width = 1; break;         // fBias / cBias
-        case 2: off = D4; width = dim; break;           // gradSqFocus / gradSqContext
-        default: off = 2 * D4 + 1; width = 1; break;    // gradSqFBias / gradSqCBias
+        case 0: off = 0; width = dim; break;             // focus / context
+        case 1: off = BO; width = 1; break;              // fBias / cBias
+        case 2: off = NS * D4; width = dim; break;       // gradSq (AdaGrad) or second moment M2 (Adam/AMSGrad)
+        case 3: off = BO + NS; width = 1; break;         // same, bias scalars
+        case 4: off = D4; width = dim; break;            // first moment M1 (Adam/AMSGrad only)
+        default: off = BO + 1; width = 1; break;         // M1 of the biases
     }
+    if (which >= 8 && NS < 2) { ctx->err = "first moments exist only for adam / amsgrad"; return GE_ERR_INVALID; }
     const size_t n = (size_t)ctx->V * width;
     float* d = nullptr;
     GE_CUDA(cudaMalloc(&d, n * sizeof(float)));

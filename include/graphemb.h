@@ -32,8 +32,9 @@ extern "C" {
 
 /* Configuration.EmbeddingMethod (J/util/config/Configuration.java:19-21) */
 enum { GE_METHOD_GLOVE = 0, GE_METHOD_PGLOVE = 1 };
-/* Configuration.OptimizationMethod (:23-25); only ADAGRAD is on the hot path this round */
-enum { GE_OPT_ADAGRAD = 0 };
+/* Configuration.OptimizationMethod (:23-25): J/opt/grad/Adagrad.java, Adam.java, AMSGrad.java.
+ * The three shipped *.config.yml select adagrad; adam / amsgrad are SURVEY §8(f) row 1. */
+enum { GE_OPT_ADAGRAD = 0, GE_OPT_ADAM = 1, GE_OPT_AMSGRAD = 2 };
 /* Configuration.BCANormalization (:31-33) */
 enum { GE_NORM_NONE = 0, GE_NORM_UNITY = 1, GE_NORM_COUNTS = 2 };
 /* Arithmetic of the AdaGrad step.
@@ -132,7 +133,8 @@ int ge_cost_history(ge_ctx*, double* out, int32_t cap); /* Optimum.costHistory; 
 int ge_extract(ge_ctx*, double* out);
 int ge_extract_f32(ge_ctx*, float* out);
 /* raw store rows in the reference's layout (validation): which = 0 focus, 1 context,
- * 2 fBias, 3 cBias, 4 gradSqFocus, 5 gradSqContext, 6 gradSqFBias, 7 gradSqCBias */
+ * 2 fBias, 3 cBias, 4 gradSqFocus, 5 gradSqContext, 6 gradSqFBias, 7 gradSqCBias (adam / amsgrad:
+ * the second moments M2*), 8 M1focus, 9 M1context, 10 M1fBias, 11 M1cBias (adam / amsgrad only) */
 int ge_store_export(ge_ctx*, int32_t which, float* out);
 /* epoch order used by the last/next epoch as an explicit permutation (validation) */
 int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);

@@ -17,6 +17,7 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 NORM = {"none": 0, "unity": 1, "counts": 2}
 METHOD = {"glove": 0, "pglove": 1}
+OPTIMIZER = {"adagrad": 0, "adam": 1, "amsgrad": 2}
 
 
 def build(force: bool = False) -> str:
@@ -52,6 +53,8 @@ def lib():
         L.orc_cooc_free.argtypes = [p]
         L.orc_train_create.argtypes = [i32, i64, p, p, p, f64, i32, i32, i64, i32]
         L.orc_train_create.restype = p
+        L.orc_train_create_opt.argtypes = [i32, i64, p, p, p, f64, i32, i32, i64, i32, i32]
+        L.orc_train_create_opt.restype = p
         L.orc_train_epoch.argtypes = [p, i32]
         L.orc_train_epoch.restype = f64
         L.orc_train_set_perm.argtypes = [p, p]
@@ -133,17 +136,20 @@ def cooc_build(csr, alpha=0.1, epsilon=1e-3, directed=True, normalize="none", th
 
 # ---- trainer ----------------------------------------------------------------------------
 class Trainer:
-    """Restatement of Optimizer + Adagrad (J/opt/Optimizer.java, J/opt/grad/Adagrad.java)."""
+    """Restatement of Optimizer + Adagrad / Adam / AMSGrad (J/opt/Optimizer.java, J/opt/grad/*.java).
+    For adam / amsgrad the gs* names are the second moments M2*, m1* the first moments."""
 
     STORE = {"focus": 0, "context": 1, "fBias": 2, "cBias": 3,
-             "gsFocus": 4, "gsContext": 5, "gsFBias": 6, "gsCBias": 7}
+             "gsFocus": 4, "gsContext": 5, "gsFBias": 6, "gsCBias": 7,
+             "m1Focus": 8, "m1Context": 9, "m1FBias": 10, "m1CBias": 11}
 
-    def __init__(self, V, I, J, X, xmax, dim, method="glove", seed=12345, threads=1):
+    def __init__(self, V, I, J, X, xmax, dim, method="glove", seed=12345, threads=1, optimizer="adagrad"):
         self.V, self.dim, self.nnz = int(V), int(dim), int(len(I))
         self._keep = (np.ascontiguousarray(I, np.int32), np.ascontiguousarray(J, np.int32),
                       np.ascontiguousarray(X, np.float32))
-        self._h = lib().orc_train_create(self.V, self.nnz, *map(_ptr, self._keep), float(xmax),
-                                         self.dim, METHOD[method], seed, threads)
+        self.optimizer = optimizer
+        self._h = lib().orc_train_create_opt(self.V, self.nnz, *map(_ptr, self._keep), float(xmax),
+                                             self.dim, METHOD[method], seed, threads, OPTIMIZER[optimizer])
 
     def epoch(self, shuffle=True) -> float:
         return lib().orc_train_epoch(self._h, int(shuffle))
@@ -171,7 +177,7 @@ class Trainer:
 
     def store(self, name) -> np.ndarray:
         w = self.STORE[name]
-        shape = (self.V,) if w in (2, 3, 6, 7) else (self.V, self.dim)
+        shape = (self.V,) if w in (2, 3, 6, 7, 10, 11) else (self.V, self.dim)
         out = np.empty(shape, np.float32)
         lib().orc_train_get_store(self._h, w, _ptr(out))
         return out

@@ -145,7 +145,7 @@ def test_errors():
     with pytest.raises(ValueError):
         cfg(method="bogus").to_native()
     c = cfg()
-    c.opt.method = "adam"
+    c.opt.method = "sgd"          # not in Configuration.OptimizationMethod (:23-25)
     with pytest.raises(ValueError):
         createOptimizer(c, None)
     with pytest.raises(GraphEmbError):

@@ -103,3 +103,73 @@ def test_hogwild_threads_slice_like_reference():
     ca = [a.epoch() for _ in range(3)]
     cb = [b.epoch() for _ in range(3)]
     assert np.allclose(ca, cb, rtol=0.02)
+
+
+def _py_epoch_adam(st, I, J, X, perm, xmax, method, iteration, amsgrad):
+    """J/opt/grad/Adam.java:75-146 / AMSGrad.java:91-162 re-derived with numpy scalar types."""
+    focus, context, fb, cb, v_f, v_c, v_fb, v_cb, m_f, m_c, m_fb, m_cb = st
+    dim = focus.shape[1]
+    b1, b2, eps, lr = f32(0.9), f32(0.999), float(f32(1e-7)), float(f32(0.05))
+    omb1, omb2 = f32(f32(1) - b1), f32(f32(1) - b2)
+    corr = lr * math.sqrt(1 - math.pow(float(b2), iteration + 1)) / (1 - math.pow(float(b1), iteration + 1))
+
+    def second(old, g2):
+        nv = f32(f32(b2 * old) + f32(omb2 * g2))
+        return (nv if old <= nv else old) if amsgrad else nv
+
+    def step(p, m, v):
+        if amsgrad:
+            return f32(float(p) - lr / (math.sqrt(float(v)) + eps) * float(m))
+        return f32(float(p) - corr * float(m) / (math.sqrt(float(v)) + eps))
+
+    cost = f32(0)
+    for k in perm:
+        u, v, x = int(I[k]), int(J[k]), f32(X[k])
+        inner = f32(0)
+        for d in range(dim):
+            inner = f32(inner + f32(focus[u, d] * context[v, d]))
+        tgt = math.log(float(x)) if method == "glove" else math.log(float(f32(x / f32(f32(1.0) - x))))
+        inner = f32(float(inner) + (float(f32(fb[u] + cb[v])) - tgt))
+        if method == "glove":
+            wc = inner if float(x) > xmax else f32(f32(math.pow(float(x) / xmax, 0.75)) * inner)
+        else:
+            wc = f32(x * inner)
+        cost = f32(float(cost) + 0.5 * float(wc) * float(inner))
+        for d in range(dim):
+            gu, gv = f32(wc * context[v, d]), f32(wc * focus[u, d])
+            m1 = f32(f32(b1 * m_f[u, d]) + f32(omb1 * gu))
+            m2 = f32(f32(b1 * m_c[v, d]) + f32(omb1 * gv))
+            v1, v2 = second(v_f[u, d], f32(gu * gu)), second(v_c[v, d], f32(gv * gv))
+            focus[u, d], context[v, d] = step(focus[u, d], m1, v1), step(context[v, d], m2, v2)
+            m_f[u, d], m_c[v, d], v_f[u, d], v_c[v, d] = m1, m2, v1, v2
+        m1 = f32(f32(b1 * m_fb[u]) + f32(omb1 * wc))
+        m2 = f32(f32(b1 * m_cb[v]) + f32(omb1 * wc))
+        w2 = f32(wc * wc)
+        v1, v2 = second(v_fb[u], w2), second(v_cb[v], w2)
+        fb[u], cb[v] = step(fb[u], m1, v1), step(cb[v], m2, v2)
+        m_fb[u], m_cb[v], v_fb[u], v_cb[v] = m1, m2, v1, v2
+    return float(cost) / len(perm)
+
+
+@pytest.mark.parametrize("optimizer", ["adam", "amsgrad"])
+@pytest.mark.parametrize("method", ["glove", "pglove"])
+def test_adam_amsgrad_match_python_rederivation(method, optimizer):
+    rng = np.random.default_rng(6)
+    V, dim, nnz, seed = 10, 4, 50, 4242
+    I = rng.integers(0, V, nnz).astype(np.int32)
+    J = rng.integers(0, V, nnz).astype(np.int32)
+    X = rng.uniform(1e-3, 0.4, nnz).astype(np.float32)
+    xmax = float(X.max())
+    t = oracle.Trainer(V, I, J, X, xmax, dim, method, seed, optimizer=optimizer)
+    focus, context, fb, cb = _init_store(V, dim, seed)
+    z = np.zeros_like
+    st = [focus, context, fb, cb, z(focus), z(context), z(fb), z(cb), z(focus), z(context), z(fb), z(cb)]
+    skip = (2 + 2 * dim) * V
+    for ep in range(1, 4):
+        perm = oracle.java_shuffle(seed, skip, nnz, ep)
+        c_py = _py_epoch_adam(st, I, J, X, perm, xmax, method, ep - 1, optimizer == "amsgrad")
+        assert t.epoch() == c_py
+    names = ["focus", "context", "fBias", "cBias", "gsFocus", "gsContext", "gsFBias", "gsCBias",
+             "m1Focus", "m1Context", "m1FBias", "m1CBias"]
+    for name, ref in zip(names, st):
+        assert np.array_equal(t.store(name), ref), name
