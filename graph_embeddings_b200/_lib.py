@@ -18,7 +18,7 @@ NORM = {"none": 0, "unity": 1, "counts": 2}
 MATH = {"fast": 0, "java": 1}
 ORDER = {"device": 0, "java": 1}
 INIT = {"counter": 0, "java": 1}
-UPDATE = {"atomic": 0, "store": 1}
+UPDATE = {"atomic": 0, "store": 1, "atomic_adam": 2}
 NCCL_ID_BYTES = 128
 
 
@@ -60,6 +60,8 @@ SIGNATURES = {
     "ge_store_export": (C.c_int, [_P, _I32, _P]),
     "ge_epoch_order": (C.c_int, [_P, _I32, _P, _I64]),
     "ge_train_stats": (C.c_int, [_P, C.POINTER(_F64), C.POINTER(_I64), C.POINTER(_I64)]),
+    "ge_write_embeddings": (C.c_int, [_P, C.c_char_p, C.c_char_p, C.c_char_p, _P, _P, _P, _P, _P, C.POINTER(_I64)]),
+    "ge_format_e": (C.c_int, [_F64, C.c_char_p, _I32]),
     "ge_dist_unique_id": (C.c_int, [_P]),
     "ge_dist_init": (C.c_int, [_P, _I32, _I32, _P]),
     "ge_dist_row_range": (C.c_int, [_P, _I32, _I32, C.POINTER(_I32), C.POINTER(_I32)]),

@@ -31,6 +31,27 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// GloveCost.innerCost :9-11 — `inner += focus[u+d] * context[v+d]` is a SEQUENTIAL f32 sum over d.
+// JAVA math reproduces that order exactly: lanes publish their four products, every lane folds
+// them in dimension order (redundantly), so the parity trajectory does not depend on a tree sum.
+template <int NT>
+__device__ __forceinline__ float dot_sequential(const float4 (&w)[NT], const float4 (&c)[NT], int nchunk) {
+    float acc = 0.f;
+#pragma unroll
+    for (int q = 0; q < NT; q++) {
+        const float px = __fmul_rn(w[q].x, c[q].x), py = __fmul_rn(w[q].y, c[q].y);
+        const float pz = __fmul_rn(w[q].z, c[q].z), pw = __fmul_rn(w[q].w, c[q].w);
+        const int live = min(32, nchunk - 32 * q);
+        for (int s = 0; s < live; s++) {
+            acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, px, s));
+            acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, py, s));
+            acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, pz, s));
+            acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, pw, s));
+        }
+    }
+    return acc;
+}
+
 // Keyed bijection on [0, n): 4-round unbalanced Feistel over ceil(log2 n) bits + cycle walking.
 // Stands in for the reference's Fisher-Yates epoch shuffle (Permutation.java:21-23) in
 // GE_ORDER_DEVICE mode: a fresh pseudo-random order per epoch with no permutation array.
@@ -119,18 +140,14 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             float2 bc = __ldcg(reinterpret_cast<const float2*>(crow + 2 * D4));
 
             float dot = 0.f;
+            if (JAVA) {
+                dot = dot_sequential<NT>(w, c, nchunk);
+            } else {
 #pragma unroll
-            for (int q = 0; q < NT; q++) {
-                if (JAVA) {  // keep f32 multiply and add separate as the JVM does
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].x, c[q].x));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].y, c[q].y));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].z, c[q].z));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].w, c[q].w));
-                } else {
+                for (int q = 0; q < NT; q++)
                     dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
-                }
+                dot = warp_sum(dot);
             }
-            dot = warp_sum(dot);
 
             float inner, wc;
             if (JAVA) {
@@ -235,15 +252,18 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
 // AMS: second moment = max(old, new) (AMSGrad.java:129-130), no bias correction, step
 // lr / (sqrt(v)+eps) * m (:133); Adam: step corr * m / (sqrt(v)+eps) (:118) with the per-epoch
 // `corr` of Adam.java:84 computed on the host in fp64.
-// FAST: f32 arithmetic; the parameter delta is applied with red.add (never lost), the moments
-// with plain stores (they are decayed averages, not sums: a lost write loses one sample, as in
-// the reference's own unsynchronised threads).  JAVA: the reference's promotion pattern.
+// FAST: f32 arithmetic, plain 128-bit stores — the reference's own racy read-modify-write
+// (last writer wins).  Unlike AdaGrad's, an Adam step is ~lr*m/sqrt(v): bounded and nearly
+// independent of the gradient's size, so ADDING the deltas of many concurrent warps on one hub
+// row (red.add, GE_UPDATE_ATOMIC_ADAM, kept for experiments) overshoots by the number of
+// concurrent writers; losing all but one of them does not.  JAVA: the reference's promotion
+// pattern (f32 moments, fp64 step).
 // ------------------------------------------------------------------------------------------
 template <int NT, bool JAVA, bool AMS>
 __global__ void __launch_bounds__(256)
 adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W, float* __restrict__ C,
             const int32_t* __restrict__ perm, Bijection bij, int32_t D4, int32_t S, int32_t method,
-            double xmax, float lr, double corr_d, double* __restrict__ cost_out) {
+            double xmax, float lr, double corr_d, int32_t atomic_p, double* __restrict__ cost_out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -292,18 +312,14 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
             float4 bw = ldcg4(wrow + BO), bc = ldcg4(crow + BO);
 
             float dot = 0.f;
+            if (JAVA) {
+                dot = dot_sequential<NT>(w, c, nchunk);
+            } else {
 #pragma unroll
-            for (int q = 0; q < NT; q++) {
-                if (JAVA) {
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].x, c[q].x));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].y, c[q].y));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].z, c[q].z));
-                    dot = __fadd_rn(dot, __fmul_rn(w[q].w, c[q].w));
-                } else {
+                for (int q = 0; q < NT; q++)
                     dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
-                }
+                dot = warp_sum(dot);
             }
-            dot = warp_sum(dot);
 
             float inner, wc;
             if (JAVA) {
@@ -338,7 +354,8 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
                     float v1 = b2 * v + omb2 * (g * g);
                     if (AMS) v1 = fmaxf(v, v1);
                     m = m1; v = v1;
-                    return -stepf * m1 / (sqrtf(v1) + epsf);
+                    const float delta = -stepf * m1 / (sqrtf(v1) + epsf);
+                    return atomic_p ? delta : p + delta;
                 }
             };
 
@@ -359,7 +376,7 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
                         wv[e] = upd(wv[e], gu, mwv[e], vwv[e]);
                         cv[e] = upd(cv[e], gv, mcv[e], vcv[e]);
                     }
-                    if (JAVA) {
+                    if (JAVA || !atomic_p) {
                         st4(wrow + 4 * ch, w[q]);
                         st4(crow + 4 * ch, c[q]);
                     } else {
@@ -375,7 +392,7 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
             if (lane == 0) {  // Adam.java:128-143 / AMSGrad.java:144-159 — biases: gradient = weightedCost
                 const float nbw = upd(bw.x, wc, bw.y, bw.z);
                 const float nbc = upd(bc.x, wc, bc.y, bc.z);
-                if (JAVA) {
+                if (JAVA || !atomic_p) {
                     bw.x = nbw; bc.x = nbc;
                     st4(wrow + BO, bw);
                     st4(crow + BO, bc);
@@ -526,16 +543,17 @@ static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStre
 
 // grid for one resident wave of kernel `k`, bounded for tiny problems (see below)
 template <typename K>
-static dim3 wave_grid(ge_ctx* ctx, K k, int64_t count, int64_t span) {
+static dim3 wave_grid(ge_ctx* ctx, K k, int64_t count, int64_t span, int ids_per_warp = 16) {
     int bps = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k, 256, 0);
     if (bps < 1) bps = 1;
     int64_t want = (count + 32 * 8 - 1) / (32 * 8);  // blocks if every warp took one batch
     int64_t full = (int64_t)ctx->sm_count * bps;     // one resident wave
     // Staleness bound for tiny problems: never more than one concurrent warp per 16 ids of
-    // the smaller side, so that a test-sized matrix sees the collision rate of a large one
-    // (at bench scale span/16 is far above a full wave and this never binds).
-    int64_t cap = span / (16 * 8);
+    // the smaller side (256 for adam / amsgrad, whose bounded sign-like steps tolerate far less
+    // staleness), so that a test-sized matrix sees the collision rate of a large one (at bench
+    // scale span/16 — or span/256 — is far above a full wave and this never binds).
+    int64_t cap = span / ((int64_t)ids_per_warp * 8);
     if (cap < 1) cap = 1;
     if (full > cap) full = cap;
     return dim3((unsigned)(want < full ? (want < 1 ? 1 : want) : full));
@@ -553,9 +571,9 @@ static int launch_adam_nt(ge_ctx* ctx, int nt, cudaStream_t st, const NzEntry* n
         auto k = adam_update<NT_, JAVA, AMS>;                                                      \
         dim3 block(256), grid;                                                                     \
         if (c.serial) { block = dim3(32); grid = dim3(1); }                                        \
-        else grid = wave_grid(ctx, k, count, span);                                                \
+        else grid = wave_grid(ctx, k, count, span, 256);                                           \
         k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax, \
-                                  c.learning_rate, corr, d_cost);                                  \
+                                  c.learning_rate, corr, c.update == GE_UPDATE_ATOMIC_ADAM, d_cost); \
     }
     switch (nt) {
         case 1: GE_LAUNCH(1); break;

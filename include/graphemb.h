@@ -58,7 +58,9 @@ enum { GE_INIT_COUNTER = 0, GE_INIT_JAVA = 1 };
  * update (only the gradient is stale, as in the reference's own Hogwild threads).
  * GE_UPDATE_STORE: plain read-modify-write stores, exactly the reference's racy pattern
  * (Adagrad.java:76-80) but with thousands of warps instead of nproc-1 threads. */
-enum { GE_UPDATE_ATOMIC = 0, GE_UPDATE_STORE = 1 };
+enum { GE_UPDATE_ATOMIC = 0, GE_UPDATE_STORE = 1, GE_UPDATE_ATOMIC_ADAM = 2 };
+/* adam / amsgrad always use plain stores unless GE_UPDATE_ATOMIC_ADAM (experiment: red.add of the
+ * parameter deltas; overshoots on hub rows, see csrc/train.cu) is selected. */
 
 typedef struct ge_config {
     int32_t dim;           /* Configuration.dim                                   */
@@ -140,6 +142,24 @@ int ge_store_export(ge_ctx*, int32_t which, float* out);
 int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);
 /* device seconds and kernel launches spent in update kernels so far */
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
+
+/* SURVEY §8(f) row 2 — EmbeddingTextWriter.write (J/util/write/EmbeddingTextWriter.java:73-149)
+ * served from the device store: <vectors_path> gets one line of "%11.6E" values (Java Formatter
+ * semantics, see ge_format_e) joined by tabs per emitted vertex, <dict_path> gets "key\tTYPE".
+ *   header        : the '#' settings block (:40-70), already formatted by the host; may be NULL
+ *   keys          : V C-strings = getKey(i); NULL (or a NULL entry) -> the decimal index
+ *   types         : V node types (0 URI, 1 BLANK, 2 LITERAL = NodeInfo ids); NULL -> all URI
+ *   type_enabled  : 3 flags = output.outputUri/Blank/LiteralNodes (:36-38); NULL -> all enabled
+ *   prefixes      : concatenated prefix lists URI | BLANK | LITERAL, nprefix[3] their lengths;
+ *                   an empty list disables the filter for that type (:114-124)
+ *   written       : number of vertices emitted */
+int ge_write_embeddings(ge_ctx*, const char* vectors_path, const char* dict_path, const char* header,
+                        const char* const* keys, const uint8_t* types, const uint8_t* type_enabled,
+                        const char* const* prefixes, const int32_t* nprefix, int64_t* written);
+/* String.format("%11.6E", v) exactly as java.util.Formatter prints a double (shortest round-trip
+ * digits rounded half-up — not C's exact-value rounding).  Returns the length, or -(needed) when
+ * cap is too small.  Pure host code: callable without a device. */
+int ge_format_e(double v, char* out, int32_t cap);
 
 /* --- multi-GPU (one process per GPU).  No reference counterpart: replaces the
  * thread slicing of J/opt/Optimizer.java:59-63 across devices. ---------------------------- */

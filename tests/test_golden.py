@@ -3,7 +3,7 @@
 not gpu: the oracle reproduces its own committed outputs bit for bit (guards the checker against
          compiler / flag / platform drift) and java.util.Random matches the public JDK answers.
 gpu    : the CUDA path, through the C ABI, reproduces the same bytes (BCA: bit-exact) or tracks
-         them (serial JAVA-math trainer: a few ulp; CUDA log/pow and the warp-tree dot differ)."""
+         them (serial JAVA-math trainer: last-bit differences of CUDA's fp64 log/pow vs libm only)."""
 import os
 
 import numpy as np
@@ -83,6 +83,6 @@ def test_gpu_serial_trainer_tracks_fixture(name):
     assert np.array_equal(opt.store("focus")[0].view(np.uint32), TRAIN[f"{name}/init_focus_row0"])
     assert np.array_equal(np.stack([opt.store("fBias"), opt.store("cBias")]).view(np.uint32), TRAIN[f"{name}/init_bias"])
     hist = np.array([opt.epoch() for _ in range(epochs)])
-    assert np.allclose(hist, TRAIN[f"{name}/history"], rtol=2e-5, atol=0), (hist, TRAIN[f"{name}/history"])
+    assert np.allclose(hist, TRAIN[f"{name}/history"], rtol=1e-6, atol=0), (hist, TRAIN[f"{name}/history"])
     assert np.array_equal(opt.epoch_order(epochs - 1), TRAIN[f"{name}/perm_last"])
-    assert np.allclose(opt.extractResultF32(), TRAIN[f"{name}/result"], rtol=5e-4, atol=5e-6)
+    assert np.allclose(opt.extractResultF32(), TRAIN[f"{name}/result"], rtol=1e-5, atol=1e-7)

@@ -61,8 +61,8 @@ def test_device_order_is_a_fresh_permutation_each_epoch():
 @pytest.mark.parametrize("method", ["glove", "pglove"])
 @pytest.mark.parametrize("dim", [10, 128, 300])
 def test_serial_java_mode_tracks_single_thread_reference(method, dim):
-    """One warp, reference order, reference promotion pattern: agrees with the 1-thread oracle to
-    a few ulp (only the warp-tree dot product and CUDA's log/pow differ)."""
+    """One warp, reference order, reference promotion pattern, sequential f32 dot: agrees with the
+    1-thread oracle up to last-bit differences of CUDA's fp64 log/pow vs libm."""
     V, nnz = 300, 4000
     I, J, X = random_coo(V, nnz, 4)
     c = cfg(method=method, dim=dim, seed=5, order="java", math="java", serial=True)
@@ -71,11 +71,12 @@ def test_serial_java_mode_tracks_single_thread_reference(method, dim):
     t = oracle.Trainer(V, I, J, X, float(X.max()), dim, method, 5)
     for ep in range(3):
         cg, co = opt.epoch(), t.epoch()
-        assert abs(cg - co) <= 1e-5 * abs(co), (ep, cg, co)
+        assert abs(cg - co) <= 1e-6 * abs(co), (ep, cg, co)
     for name in STORE:
         a, b = opt.store(name), t.store(name)
-        assert np.allclose(a, b, rtol=2e-4, atol=2e-6), name
-    assert np.allclose(opt.extractResult(), t.extract(), rtol=2e-4, atol=2e-6)
+        assert np.allclose(a, b, rtol=1e-5, atol=1e-7), (name, np.abs(a - b).max())
+        print(name, "bit-equal fraction", float(np.mean(a == b)))
+    assert np.allclose(opt.extractResult(), t.extract(), rtol=1e-5, atol=1e-7)
 
 
 def _nn_overlap(A, B, sample, k=10):
