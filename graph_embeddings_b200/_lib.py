@@ -43,6 +43,9 @@ SIGNATURES = {
     "ge_version": (C.c_char_p, []),
     "ge_set_stream": (C.c_int, [_P, _P]),
     "ge_set_graph_csr": (C.c_int, [_P, _I32, _P, _P, _P, _P, _P, _P]),
+    "ge_set_graph_edges": (C.c_int, [_P, _I32, _I64, _P, _P, _P]),
+    "ge_graph_sizes": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64), C.POINTER(_F64)]),
+    "ge_graph_export": (C.c_int, [_P, _P, _P, _P, _P, _P, _P]),
     "ge_cooc_build": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_cooc_build_rows": (C.c_int, [_P, _I32, _I32, C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_cooc_stats": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64), C.POINTER(_F64)]),

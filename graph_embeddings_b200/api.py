@@ -168,10 +168,15 @@ class BookmarkColoring(CoOccurrenceMatrix):
         self._n = _Native(config)
         n, L = self._n, self._n.L
         g = graph
-        arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
-                np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
-                np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
-        n.ck(L.ge_set_graph_csr(n.h, g.V, *map(_ptr, arrs)))
+        if hasattr(g, "src"):       # raw edge list: adjacency flattening on the device (ge_set_graph_edges)
+            arrs = [np.ascontiguousarray(g.src, np.int32), np.ascontiguousarray(g.dst, np.int32),
+                    np.ascontiguousarray(g.w, np.float32)]
+            n.ck(L.ge_set_graph_edges(n.h, g.V, len(arrs[0]), *map(_ptr, arrs)))
+        else:
+            arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
+                    np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
+                    np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
+            n.ck(L.ge_set_graph_csr(n.h, g.V, *map(_ptr, arrs)))
         nnz, xmax = C.c_int64(0), C.c_double(0)
         if rows is None:
             n.ck(L.ge_cooc_build(n.h, C.byref(nnz), C.byref(xmax)))
@@ -217,6 +222,17 @@ class BookmarkColoring(CoOccurrenceMatrix):
         pops, scanned, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
         self._n.ck(self._n.L.ge_cooc_stats(self._n.h, C.byref(pops), C.byref(scanned), C.byref(sec)))
         return {"pops": pops.value, "scanned": scanned.value, "seconds": sec.value, "nnz": self._nnz}
+
+    def graph_csr(self):
+        """The hand-off CSR as it sits on the device (validation of ge_set_graph_edges):
+        (out_off, out_nbr, out_w, in_off, in_nbr, in_w, flatten_seconds)."""
+        n, L = self._n, self._n.L
+        eo, ei, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
+        n.ck(L.ge_graph_sizes(n.h, C.byref(eo), C.byref(ei), C.byref(sec)))
+        a = [np.empty(self._V + 1, np.int64), np.empty(eo.value, np.int32), np.empty(eo.value, np.float32),
+             np.empty(self._V + 1, np.int64), np.empty(ei.value, np.int32), np.empty(ei.value, np.float32)]
+        n.ck(L.ge_graph_export(n.h, *map(_ptr, a)))
+        return (*a, sec.value)
 
 
 class ImportedMatrix(BookmarkColoring):

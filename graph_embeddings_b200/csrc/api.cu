@@ -42,14 +42,6 @@ __global__ void max_f32(const float* __restrict__ X, int64_t n, float* __restric
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int*>(out), __float_as_int(m));
 }
 
-void free_graph(ge_ctx* ctx) {
-    cudaFree(ctx->d_out_off); cudaFree(ctx->d_in_off); cudaFree(ctx->d_out_nbr); cudaFree(ctx->d_in_nbr);
-    cudaFree(ctx->d_out_w); cudaFree(ctx->d_in_w); cudaFree(ctx->d_out_total); cudaFree(ctx->d_in_total);
-    cudaFree(ctx->d_out_wmax); cudaFree(ctx->d_in_wmax); ctx->d_out_wmax = ctx->d_in_wmax = nullptr;
-    ctx->d_out_off = ctx->d_in_off = nullptr; ctx->d_out_nbr = ctx->d_in_nbr = nullptr;
-    ctx->d_out_w = ctx->d_in_w = nullptr; ctx->d_out_total = ctx->d_in_total = nullptr;
-}
-
 int check_csr(ge_ctx* ctx, int32_t V, const int64_t* off, const int32_t* nbr, const char* name) {
     if (off[0] != 0) { ctx->err = std::string(name) + "_off[0] != 0"; return GE_ERR_GRAPH; }
     for (int32_t v = 0; v < V; v++) {
@@ -66,6 +58,28 @@ int check_csr(ge_ctx* ctx, int32_t V, const int64_t* off, const int32_t* nbr, co
 }
 
 }  // namespace
+
+void ge_free_graph(ge_ctx* ctx) {
+    cudaFree(ctx->d_out_off); cudaFree(ctx->d_in_off); cudaFree(ctx->d_out_nbr); cudaFree(ctx->d_in_nbr);
+    cudaFree(ctx->d_out_w); cudaFree(ctx->d_in_w); cudaFree(ctx->d_out_total); cudaFree(ctx->d_in_total);
+    cudaFree(ctx->d_out_wmax); cudaFree(ctx->d_in_wmax); ctx->d_out_wmax = ctx->d_in_wmax = nullptr;
+    ctx->d_out_off = ctx->d_in_off = nullptr; ctx->d_out_nbr = ctx->d_in_nbr = nullptr;
+    ctx->d_out_w = ctx->d_in_w = nullptr; ctx->d_out_total = ctx->d_in_total = nullptr;
+    ctx->E_out = ctx->E_in = 0;
+}
+
+// per-node fp64 weight totals + heaviest edge for the CSR now on the device (both hand-off paths)
+int ge_graph_finish(ge_ctx* ctx) {
+    const int32_t V = ctx->V;
+    cudaFree(ctx->d_out_total); cudaFree(ctx->d_in_total); cudaFree(ctx->d_out_wmax); cudaFree(ctx->d_in_wmax);
+    ctx->d_out_total = ctx->d_in_total = nullptr; ctx->d_out_wmax = ctx->d_in_wmax = nullptr;
+    node_totals<<<(V + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_out_off, ctx->d_out_w, ctx->d_in_off, ctx->d_in_w, V,
+                                                          ctx->cfg.directed, ctx->d_out_total, ctx->d_in_total,
+                                                          ctx->d_out_wmax, ctx->d_in_wmax);
+    GE_CUDA(cudaGetLastError());
+    GE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return GE_OK;
+}
 
 extern "C" void ge_config_default(ge_config* c) {
     if (!c) return;
@@ -143,7 +157,7 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     ge_dist_free(ctx);
     ge_free_store(ctx);
     ge_free_cooc(ctx);
-    free_graph(ctx);
+    ge_free_graph(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -160,7 +174,7 @@ extern "C" int ge_set_graph_csr(ge_ctx* ctx, int32_t V, const int64_t* out_off, 
     if (r) return r;
     r = check_csr(ctx, V, in_off, in_nbr, "in");
     if (r) return r;
-    free_graph(ctx);
+    ge_free_graph(ctx);
     ge_free_cooc(ctx);
     ge_free_store(ctx);
     ctx->V = V;
@@ -173,10 +187,6 @@ extern "C" int ge_set_graph_csr(ge_ctx* ctx, int32_t V, const int64_t* out_off, 
     GE_CUDA(cudaMalloc(&ctx->d_out_w, (size_t)(ctx->E_out + 1) * 4));
     GE_CUDA(cudaMalloc(&ctx->d_in_nbr, (size_t)(ctx->E_in + 1) * 4));
     GE_CUDA(cudaMalloc(&ctx->d_in_w, (size_t)(ctx->E_in + 1) * 4));
-    GE_CUDA(cudaMalloc(&ctx->d_out_total, (size_t)V * 8));
-    GE_CUDA(cudaMalloc(&ctx->d_in_total, (size_t)V * 8));
-    GE_CUDA(cudaMalloc(&ctx->d_out_wmax, (size_t)V * 4));
-    GE_CUDA(cudaMalloc(&ctx->d_in_wmax, (size_t)V * 4));
     cudaStream_t s = ctx->stream;
     GE_CUDA(cudaMemcpyAsync(ctx->d_out_off, out_off, ob, cudaMemcpyHostToDevice, s));
     GE_CUDA(cudaMemcpyAsync(ctx->d_in_off, in_off, ob, cudaMemcpyHostToDevice, s));
@@ -188,12 +198,9 @@ extern "C" int ge_set_graph_csr(ge_ctx* ctx, int32_t V, const int64_t* out_off, 
         GE_CUDA(cudaMemcpyAsync(ctx->d_in_nbr, in_nbr, (size_t)ctx->E_in * 4, cudaMemcpyHostToDevice, s));
         GE_CUDA(cudaMemcpyAsync(ctx->d_in_w, in_w, (size_t)ctx->E_in * 4, cudaMemcpyHostToDevice, s));
     }
-    node_totals<<<(V + 127) / 128, 128, 0, s>>>(ctx->d_out_off, ctx->d_out_w, ctx->d_in_off, ctx->d_in_w, V,
-                                                ctx->cfg.directed, ctx->d_out_total, ctx->d_in_total,
-                                                ctx->d_out_wmax, ctx->d_in_wmax);
-    GE_CUDA(cudaGetLastError());
     GE_CUDA(cudaStreamSynchronize(s));
-    return GE_OK;
+    ctx->graph_seconds = 0;
+    return ge_graph_finish(ctx);
 }
 
 void ge_free_cooc(ge_ctx* ctx) {

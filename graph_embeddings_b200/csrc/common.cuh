@@ -71,6 +71,7 @@ struct ge_ctx {
     // --- graph (A1) ---
     int32_t V = 0;
     int64_t E_out = 0, E_in = 0;
+    double graph_seconds = 0;  // device time of the last edge-list flattening
     int64_t *d_out_off = nullptr, *d_in_off = nullptr;
     int32_t *d_out_nbr = nullptr, *d_in_nbr = nullptr;
     float *d_out_w = nullptr, *d_in_w = nullptr;
@@ -116,6 +117,9 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
 void ge_free_store(ge_ctx* ctx);
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
+// api.cu
+void ge_free_graph(ge_ctx* ctx);
+int ge_graph_finish(ge_ctx* ctx);
 // bca.cu
 int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);
 void ge_free_cooc(ge_ctx* ctx);

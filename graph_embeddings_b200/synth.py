@@ -33,6 +33,18 @@ class CsrGraph:
         return int(self.out_nbr.shape[0])
 
 
+@dataclass
+class EdgeList:
+    """Raw directed edge list (parallel edges allowed) — the input of the device-side adjacency
+    flattening (ge_set_graph_edges), i.e. the graph BEFORE getIn/OutNeighborhoods and
+    In/OutEdgeNeighborhoodAlgorithm.compute (J/bca/BookmarkColoring.java:49-52)."""
+
+    V: int
+    src: np.ndarray
+    dst: np.ndarray
+    w: np.ndarray
+
+
 def csr_from_edges(V: int, src, dst, w) -> CsrGraph:
     """Build both CSRs from an edge list; duplicates (s,d) keep the first weight, order by id."""
     src = np.asarray(src, np.int64)

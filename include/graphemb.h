@@ -106,6 +106,17 @@ int ge_set_graph_csr(ge_ctx*, int32_t V, const int64_t* out_off, const int32_t* 
                      const float* out_w, const int64_t* in_off, const int32_t* in_nbr,
                      const float* in_w);
 
+/* SURVEY §8(f) row 3 — the same hand-off computed ON THE DEVICE from the raw directed edge list
+ * (replaces getIn/OutNeighborhoods + In/OutEdgeNeighborhoodAlgorithm.compute,
+ * J/convert/util/EdgeNeighborhoodAlgorithm.java:42-77).  Parallel edges collapse to one neighbour
+ * whose weight is that of the first such edge in input order; self-loops are kept. */
+int ge_set_graph_edges(ge_ctx*, int32_t V, int64_t E, const int32_t* src, const int32_t* dst, const float* w);
+/* sizes of the CSR now on the device (unique out- / in-neighbour entries), seconds spent flattening */
+int ge_graph_sizes(ge_ctx*, int64_t* E_out, int64_t* E_in, double* flatten_seconds);
+/* copy the device CSR back (validation); any pointer may be NULL */
+int ge_graph_export(ge_ctx*, int64_t* out_off, int32_t* out_nbr, float* out_w, int64_t* in_off,
+                    int32_t* in_nbr, float* in_w);
+
 /* A2-A4 — new BookmarkColoring(graph, config): builds the COO on the device.
  * Outputs: nnz = coOccurrenceCount(), xmax = max().  Rows [first, first+count) only when
  * count >= 0 (multi-GPU row sharding); count < 0 = all rows. */

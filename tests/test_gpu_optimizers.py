@@ -60,8 +60,10 @@ def test_fast_hogwild_converges_like_reference(optimizer, method):
     an AdaGrad bar (tests/test_gpu_train.py).  An Adam-type step is ~lr*m/sqrt(v), i.e. of size
     ~3*lr whatever the gradient, so the early trajectory is chaotic in the REFERENCE ITSELF (its
     single-thread AMSGrad loss rises 4x in epoch 2 before falling) and no different execution
-    order can track it epoch by epoch.  What must hold: finite, decreasing, and the loss after
-    the last epoch no worse than 1.5x the single-thread reference's."""
+    order can track it to 1 %: the reference run with its own 15 Hogwild threads deviates from
+    its single-thread run by up to ~5 % mid-trajectory (printed).  Bar: every epoch within 20 %
+    (or 3x the reference's own thread-noise) and the last epoch within 5 %.  Concurrency on tiny
+    problems is bounded to one warp per 256 ids (csrc/train.cu wave_grid)."""
     g = synth.rmat(8000, 64000, 4)
     dim, epochs = 32, 12
     c = cfg(optimizer, method=method, dim=dim, maxiter=epochs, seed=31, order="java")
@@ -73,4 +75,6 @@ def test_fast_hogwild_converges_like_reference(optimizer, method):
     th, _ = oracle.Trainer(g.V, I, J, X, bca.max(), dim, method, 31, optimizer=optimizer, threads=15).optimize(epochs, 0.0)
     print(optimizer, method, "gpu", np.round(got, 5), "ref", np.round(hist, 5), "ref 15 threads", np.round(th, 5))
     assert len(got) == epochs and np.isfinite(got).all()
-    assert got[-1] < got[0] and got[-1] <= 1.5 * hist[-1], (got, hist)
+    rel = np.abs(got - hist) / hist
+    rel_t = np.abs(th - hist) / hist          # the reference against itself with 15 Hogwild threads
+    assert rel.max() < max(0.2, 3 * rel_t.max()) and rel[-1] < 0.05, (rel, rel_t)
