@@ -96,7 +96,7 @@ def make_graph(V, E, use_cuda):
     return g
 
 
-def cpu_baseline(g, dim, steps, warmup, threads, target_nnz=3_000_000):
+def cpu_baseline(g, dim, steps, warmup, threads, target_nnz=12_000_000):
     """The oracle (C++ restatement of the Java path — NOT a JVM; see oracle/oracle.cpp) timed on
     the host cores: Hogwild with `threads` threads (reference default nproc-1,
     Configuration.java:71-73) on a bounded sample = the co-occurrence rows of the first S
@@ -219,7 +219,7 @@ def run_single(args):
     cb = None
     if not args.no_cpu_baseline:
         threads = max(1, (os.cpu_count() or 2) - 1)
-        cb = cpu_baseline(g, dim, 2, 1, threads)
+        cb = cpu_baseline(g, dim, 6, 1, threads)          # ~10-20 s of host work
 
     build_bytes = 8 * cst["scanned"] + 8 * cst["pops"] + 12 * nnz
     line = {"metric": "glove_nnz_updates_per_sec", "value": nnz * K / (ms * 1e-3), "unit": "nnz_updates/s",

@@ -73,6 +73,10 @@ int ge_graph_finish(ge_ctx* ctx) {
     const int32_t V = ctx->V;
     cudaFree(ctx->d_out_total); cudaFree(ctx->d_in_total); cudaFree(ctx->d_out_wmax); cudaFree(ctx->d_in_wmax);
     ctx->d_out_total = ctx->d_in_total = nullptr; ctx->d_out_wmax = ctx->d_in_wmax = nullptr;
+    GE_CUDA(cudaMalloc(&ctx->d_out_total, (size_t)V * 8));
+    GE_CUDA(cudaMalloc(&ctx->d_in_total, (size_t)V * 8));
+    GE_CUDA(cudaMalloc(&ctx->d_out_wmax, (size_t)V * 4));
+    GE_CUDA(cudaMalloc(&ctx->d_in_wmax, (size_t)V * 4));
     node_totals<<<(V + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_out_off, ctx->d_out_w, ctx->d_in_off, ctx->d_in_w, V,
                                                           ctx->cfg.directed, ctx->d_out_total, ctx->d_in_total,
                                                           ctx->d_out_wmax, ctx->d_in_wmax);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <string>
 #include <vector>
@@ -14,6 +15,20 @@
         if (e__ != cudaSuccess) {                                                            \
             ctx->err = std::string(#call) + ": " + cudaGetErrorString(e__);                  \
             return e__ == cudaErrorMemoryAllocation ? GE_ERR_NOMEM : GE_ERR_CUDA;            \
+        }                                                                                    \
+    } while (0)
+
+// GE_DEBUG=1 in the environment: synchronise after the named step and report which one faulted
+#define GE_DBG(name)                                                                         \
+    do {                                                                                     \
+        static const bool dbg__ = getenv("GE_DEBUG") != nullptr;                             \
+        if (dbg__) {                                                                         \
+            cudaError_t e__ = cudaStreamSynchronize(ctx->stream);                            \
+            if (e__ == cudaSuccess) e__ = cudaGetLastError();                                \
+            if (e__ != cudaSuccess) {                                                        \
+                ctx->err = std::string(name) + ": " + cudaGetErrorString(e__);               \
+                return GE_ERR_CUDA;                                                          \
+            }                                                                                \
         }                                                                                    \
     } while (0)
 

@@ -246,15 +246,20 @@ static int build_direction(ge_ctx* ctx, const int32_t* d_src, const int32_t* d_d
     uint32_t* d_total = (uint32_t*)(bad + 1);
     GE_CUDA(cudaMemsetAsync(bad, 0, 16, st));
     pack_keys<<<ctx->sm_count * 8, 256, 0, st>>>(d_src, d_dst, E, V, idbits, by_dst, k0, v0, bad);
+    GE_DBG("pack_keys");
     for (int shift = 0; shift < 2 * idbits; shift += 8) {
         rs_hist<<<nb, RS_THREADS, 0, st>>>(k0, E, shift, hist, nb);
+        GE_DBG("rs_hist");
         int r = device_scan(ctx, hist, (int64_t)hist_n, hist, sums, nullptr);
         if (r) return r;
+        GE_DBG("scan(hist)");
         rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, E, shift, hist, nb, k1, v1);
+        GE_DBG("rs_scatter");
         std::swap(k0, k1);
         std::swap(v0, v1);
     }
     flag_heads<<<ctx->sm_count * 8, 256, 0, st>>>(k0, E, flag);
+    GE_DBG("flag_heads");
     uint32_t* pos = v1;  // the spare value buffer holds the scanned positions
     int r = device_scan(ctx, flag, E, pos, sums, d_total);
     if (r) return r;
@@ -270,6 +275,7 @@ static int build_direction(ge_ctx* ctx, const int32_t* d_src, const int32_t* d_d
     }
     uint64_t* ukeys = k1;  // spare key buffer
     compact_heads<<<ctx->sm_count * 8, 256, 0, st>>>(k0, v0, flag, pos, E, idbits, d_w, ukeys, nbr, w);
+    GE_DBG("compact_heads");
     offsets_by_search<<<(V + 1 + 255) / 256, 256, 0, st>>>(ukeys, m, V, idbits, off);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -316,6 +322,7 @@ extern "C" int ge_set_graph_edges(ge_ctx* ctx, int32_t V, int64_t E, const int32
         if (r) { ge_free_graph(ctx); return r; }
     }
     GE_CUDA(cudaEventRecord(ctx->ev1, st));
+    GE_DBG("flatten");
     int r = ge_graph_finish(ctx);
     if (r) return r;
     float ms = 0;

@@ -25,6 +25,14 @@ __device__ __forceinline__ void red2(float* p, float a, float b) {
     asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
 }
 
+// Bulk L2 prefetch of one whole store row (vec | gradsq | bias block: S*4 contiguous bytes, 16-B
+// aligned) issued by ONE lane through the bulk-copy (TMA) engine: the row of the nonzero `pf`
+// steps ahead is in L2 when its LDG.128s issue, which raises memory-level parallelism without
+// spending registers on a second row set.
+__device__ __forceinline__ void prefetch_row_l2(const float* row, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(row), "r"(bytes) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -91,10 +99,10 @@ struct Bijection {
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
 template <int NT, bool JAVA, bool ATOMIC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
-                     int32_t D4, int32_t S, int32_t method, double xmax, float lr,
+                     int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
                      double* __restrict__ cost_out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -104,17 +112,35 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
     double cost_d = 0.0;
     float cost_f = 0.0f;  // JAVA: the reference's f32 running cost (Adagrad.java:46,60)
 
-    for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
-        // lane l fetches the nonzero at shuffled position base + l
-        NzEntry mine = {0, 0, 0.f, 0.f};
-        const int64_t pos = base + lane;
+    auto fetch = [&](int64_t pos) -> NzEntry {  // lane l fetches the nonzero at shuffled position pos
+        NzEntry e = {0, 0, 0.f, 0.f};
         if (pos < count) {
             const int64_t idx = perm ? (int64_t)perm[pos] : (int64_t)bij((uint64_t)pos);
             const int4 raw = __ldg(reinterpret_cast<const int4*>(nz + idx));
-            mine.i = raw.x; mine.j = raw.y; mine.a = __int_as_float(raw.z); mine.b = __int_as_float(raw.w);
+            e.i = raw.x; e.j = raw.y; e.a = __int_as_float(raw.z); e.b = __int_as_float(raw.w);
         }
+        return e;
+    };
+    const uint32_t row_bytes = (uint32_t)S * 4u;
+    NzEntry mine = fetch(warp * 32 + lane);
+    for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
+        const int64_t next_base = base + nwarps * 32;
+        const NzEntry nxt = fetch(next_base + lane);  // next batch: issued now, needed 32 nonzeros later
         const int nvalid = (int)min((int64_t)32, count - base);
         for (int t = 0; t < nvalid; t++) {
+            if (pf > 0) {  // warp-uniform
+                const int tt = t + pf;
+                int32_t pi, pj;
+                bool ok;
+                if (tt < 32) {
+                    pi = __shfl_sync(0xffffffffu, mine.i, tt); pj = __shfl_sync(0xffffffffu, mine.j, tt);
+                    ok = base + tt < count;
+                } else {
+                    pi = __shfl_sync(0xffffffffu, nxt.i, tt - 32); pj = __shfl_sync(0xffffffffu, nxt.j, tt - 32);
+                    ok = next_base + (tt - 32) < count;
+                }
+                if (ok && lane < 2) prefetch_row_l2(lane == 0 ? W + (size_t)pi * S : C + (size_t)pj * S, row_bytes);
+            }
             const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
             const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
@@ -238,6 +264,7 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             }
             if (JAVA) __syncwarp();  // serial order: lane 0's bias store precedes the next loads
         }
+        mine = nxt;
     }
     if (lane == 0) {
         const double cst = JAVA ? (double)cost_f : cost_d;
@@ -518,6 +545,13 @@ uint64_t epoch_key(int64_t seed, int32_t epoch) {
 // ==========================================================================================
 // host side
 // ==========================================================================================
+// rows prefetched into L2 this many nonzeros ahead (GE_PF_DIST overrides; 0 = off; max 32)
+static int ge_prefetch_distance() {
+    const char* e = getenv("GE_PF_DIST");  // read per launch: a development sweep can change it between epochs
+    const int v = e ? atoi(e) : 0;
+    return v < 0 ? 0 : (v > 32 ? 32 : v);
+}
+
 template <bool JAVA, bool ATOMIC>
 static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStream_t st,
                             const NzEntry* nz, int64_t count, float* W, float* C,
@@ -526,7 +560,7 @@ static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStre
 #define GE_LAUNCH(NT_)                                                                            \
     glove_adagrad_update<NT_, JAVA, ATOMIC><<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4,  \
                                                             ctx->S, c.method, ctx->xmax,         \
-                                                            c.learning_rate, d_cost)
+                                                            c.learning_rate, ge_prefetch_distance(), d_cost)
     switch (nt) {
         case 1: GE_LAUNCH(1); break;
         case 2: GE_LAUNCH(2); break;
