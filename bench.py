@@ -29,6 +29,8 @@ WORKLOADS = {
     # name: (V, E, dim, description)
     "c4": (10_000_000, 100_000_000, 128, "R-MAT 10M nodes / 100M edges, d=128 (BASELINE configs[3])"),
     "c3": (2_000_000, 20_000_000, 128, "R-MAT 2M nodes / 20M edges, d=128 (BASELINE configs[2])"),
+    # configs[4]: direct COO, multi-GPU only (store 243 GB at d=300); "E" = nonzeros at 8 GPUs
+    "c5": (50_000_000, 1_000_000_000, 300, "synthetic COO 50M rows / 1e9 nonzeros, d=300 (BASELINE configs[4])"),
     "small": (200_000, 2_000_000, 128, "R-MAT 200k nodes / 2M edges, d=128 (smoke-sized)"),
 }
 ALPHA, EPS, SEED = 0.1, 1e-3, 5
@@ -260,7 +262,7 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world > 1 or args.gpus > 1:
+    if world > 1 or args.gpus > 1 or args.workload == "c5":
         from graph_embeddings_b200 import dist_bench
         return dist_bench.run(args, WORKLOADS, (ALPHA, EPS, SEED), log, peaks, ClockSampler, make_graph)
     return run_single(args)

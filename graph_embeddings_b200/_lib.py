@@ -7,7 +7,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgraphemb.so")
+LIB_PATH = os.environ.get("GE_LIB") or os.path.join(_HERE, "libgraphemb.so")  # GE_LIB: development builds
 
 GE_OK = 0
 ERRORS = {-1: "GE_ERR_INVALID", -2: "GE_ERR_STATE", -3: "GE_ERR_CUDA", -4: "GE_ERR_NOMEM",

@@ -15,6 +15,18 @@
 namespace {
 
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+// order-pinned variants (asm volatile statements keep their program order): used to fix WHEN the
+// row loads issue relative to the dot-product reduction (GE_LOAD_ORDER, see the kernel)
+__device__ __forceinline__ float4 ldcg4v(const float* p) {
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 ldcg2v(const float* p) {
+    float2 v;
+    asm volatile("ld.global.cg.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 // vector float reduction at L2 (sm_90+): no value returns to the SM, updates are never lost
@@ -31,6 +43,10 @@ __device__ __forceinline__ void red2(float* p, float a, float b) {
 // spending registers on a second row set.
 __device__ __forceinline__ void prefetch_row_l2(const float* row, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(row), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void prefetch_line_l2(const float* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory");
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -98,7 +114,7 @@ struct Bijection {
 // K6 — the update kernel.  NT = float4 chunks per lane per vector (dim <= 128*NT).
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
-template <int NT, bool JAVA, bool ATOMIC>
+template <int NT, bool JAVA, bool ATOMIC, bool TP>
 __global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
@@ -122,6 +138,9 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
         return e;
     };
     const uint32_t row_bytes = (uint32_t)S * 4u;
+    constexpr bool two_phase = TP;  // launcher: D4 >= 128 (rows at least one warp of float4 wide)
+    const bool pf_lines = pf >= 100;  // GE_PF_DIST = 100 + distance selects prefetch.global.L2 per line
+    if (pf_lines) pf -= 100;
     NzEntry mine = fetch(warp * 32 + lane);
     for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
         const int64_t next_base = base + nwarps * 32;
@@ -139,7 +158,15 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     pi = __shfl_sync(0xffffffffu, nxt.i, tt - 32); pj = __shfl_sync(0xffffffffu, nxt.j, tt - 32);
                     ok = next_base + (tt - 32) < count;
                 }
-                if (ok && lane < 2) prefetch_row_l2(lane == 0 ? W + (size_t)pi * S : C + (size_t)pj * S, row_bytes);
+                if (ok) {
+                    if (pf_lines) {  // per-line variant: lanes 0..15 cover the W row, 16..31 the C row (128 B each)
+                        const int l = lane & 15;
+                        if ((uint32_t)l * 128u < row_bytes)
+                            prefetch_line_l2((lane < 16 ? W + (size_t)pi * S : C + (size_t)pj * S) + l * 32);
+                    } else if (lane < 2) {
+                        prefetch_row_l2(lane == 0 ? W + (size_t)pi * S : C + (size_t)pj * S, row_bytes);
+                    }
+                }
             }
             const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
             const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
@@ -149,30 +176,52 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             float* crow = C + (size_t)bj * S;
 
             float4 w[NT], c[NT], gw[NT], gc[NT];
-#pragma unroll
-            for (int q = 0; q < NT; q++) {
-                const int ch = lane + 32 * q;
-                if (ch < nchunk) {
-                    w[q] = ldcg4(wrow + 4 * ch);
-                    c[q] = ldcg4(crow + 4 * ch);
-                    gw[q] = ldcg4(wrow + D4 + 4 * ch);
-                    gc[q] = ldcg4(crow + D4 + 4 * ch);
-                } else {
-                    w[q] = c[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    gw[q] = gc[q] = make_float4(1.f, 1.f, 1.f, 1.f);
-                }
-            }
-            float2 bw = __ldcg(reinterpret_cast<const float2*>(wrow + 2 * D4));  // (bias, gradsq)
-            float2 bc = __ldcg(reinterpret_cast<const float2*>(crow + 2 * D4));
-
+            float2 bw, bc;
             float dot = 0.f;
             if (JAVA) {
+#pragma unroll
+                for (int q = 0; q < NT; q++) {
+                    const int ch = lane + 32 * q;
+                    if (ch < nchunk) {
+                        w[q] = ldcg4(wrow + 4 * ch);
+                        c[q] = ldcg4(crow + 4 * ch);
+                        gw[q] = ldcg4(wrow + D4 + 4 * ch);
+                        gc[q] = ldcg4(crow + D4 + 4 * ch);
+                    } else {
+                        w[q] = c[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        gw[q] = gc[q] = make_float4(1.f, 1.f, 1.f, 1.f);
+                    }
+                }
+                bw = __ldcg(reinterpret_cast<const float2*>(wrow + 2 * D4));  // (bias, gradsq)
+                bc = __ldcg(reinterpret_cast<const float2*>(crow + 2 * D4));
                 dot = dot_sequential<NT>(w, c, nchunk);
             } else {
+                // Issue order of the row loads is pinned (asm volatile).  two_phase: the vectors
+                // first, the AdaGrad rows + bias pairs only after the dot-product reduction —
+                // measured on B200 (C3 graph): d=128 134.4 vs 141.8 ms, d=300 325 vs 370 ms per
+                // epoch; for rows narrower than a warp (d=100: 119.8 vs 107.7 ms) everything up
+                // front is faster, so the launcher picks by D4 (profiles/r01_load_order.md).
+                auto ldv = [&](float4 (&a)[NT], const float* base, float fill) {
+#pragma unroll
+                    for (int q = 0; q < NT; q++) {
+                        const int ch = lane + 32 * q;
+                        a[q] = ch < nchunk ? ldcg4v(base + 4 * ch) : make_float4(fill, fill, fill, fill);
+                    }
+                };
+                ldv(w, wrow, 0.f);
+                ldv(c, crow, 0.f);
+                if (!two_phase) {
+                    ldv(gw, wrow + D4, 1.f); ldv(gc, crow + D4, 1.f);
+                    bw = ldcg2v(wrow + 2 * D4); bc = ldcg2v(crow + 2 * D4);
+                }
 #pragma unroll
                 for (int q = 0; q < NT; q++)
                     dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
                 dot = warp_sum(dot);
+                if (two_phase) {
+                    ldv(gw, wrow + D4, 1.f); ldv(gc, crow + D4, 1.f);
+                    bw = ldcg2v(wrow + 2 * D4); bc = ldcg2v(crow + 2 * D4);
+                }
             }
 
             float inner, wc;
@@ -549,30 +598,7 @@ uint64_t epoch_key(int64_t seed, int32_t epoch) {
 static int ge_prefetch_distance() {
     const char* e = getenv("GE_PF_DIST");  // read per launch: a development sweep can change it between epochs
     const int v = e ? atoi(e) : 0;
-    return v < 0 ? 0 : (v > 32 ? 32 : v);
-}
-
-template <bool JAVA, bool ATOMIC>
-static int launch_update_nt(ge_ctx* ctx, int nt, dim3 grid, dim3 block, cudaStream_t st,
-                            const NzEntry* nz, int64_t count, float* W, float* C,
-                            const int32_t* perm, Bijection bij, double* d_cost) {
-    const ge_config& c = ctx->cfg;
-#define GE_LAUNCH(NT_)                                                                            \
-    glove_adagrad_update<NT_, JAVA, ATOMIC><<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4,  \
-                                                            ctx->S, c.method, ctx->xmax,         \
-                                                            c.learning_rate, ge_prefetch_distance(), d_cost)
-    switch (nt) {
-        case 1: GE_LAUNCH(1); break;
-        case 2: GE_LAUNCH(2); break;
-        case 3: GE_LAUNCH(3); break;
-        case 4: GE_LAUNCH(4); break;
-        case 6: GE_LAUNCH(6); break;
-        case 8: GE_LAUNCH(8); break;
-        default: ctx->err = "dim too large (max 1024)"; return GE_ERR_INVALID;
-    }
-#undef GE_LAUNCH
-    GE_CUDA(cudaGetLastError());
-    return GE_OK;
+    return v < 0 ? 0 : ((v % 100) > 32 ? 0 : v);
 }
 
 // grid for one resident wave of kernel `k`, bounded for tiny problems (see below)
@@ -638,22 +664,35 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
         return ams ? launch_adam_nt<false, true>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span)
                    : launch_adam_nt<false, false>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span);
     }
-    dim3 block(256), grid;
-    if (ctx->cfg.serial) { block = dim3(32); grid = dim3(1); }
-    else {
-        switch (nt) {
-#define GE_GRID(NT_) case NT_: grid = java ? wave_grid(ctx, glove_adagrad_update<NT_, true, false>, count, span) \
-                                          : wave_grid(ctx, glove_adagrad_update<NT_, false, true>, count, span); break;
-            GE_GRID(1) GE_GRID(2) GE_GRID(3) GE_GRID(4) GE_GRID(6)
-            default: grid = java ? wave_grid(ctx, glove_adagrad_update<8, true, false>, count, span)
-                                 : wave_grid(ctx, glove_adagrad_update<8, false, true>, count, span); break;
-#undef GE_GRID
-        }
+    const int pf = ge_prefetch_distance();
+    const ge_config& c = ctx->cfg;
+    // one instantiation per (NT, math, update mode, load order); grid = one resident wave
+#define GE_GO(NT_, JAVA_, ATOMIC_, TP_)                                                                   \
+    {                                                                                                     \
+        auto k = glove_adagrad_update<NT_, JAVA_, ATOMIC_, TP_>;                                          \
+        dim3 block(256), grid;                                                                            \
+        if (c.serial) { block = dim3(32); grid = dim3(1); }                                               \
+        else grid = wave_grid(ctx, k, count, span);                                                       \
+        k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax,       \
+                                  c.learning_rate, pf, d_cost);                                           \
     }
-    if (java) return launch_update_nt<true, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
-    if (ctx->cfg.update == GE_UPDATE_STORE)
-        return launch_update_nt<false, false>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
-    return launch_update_nt<false, true>(ctx, nt, grid, block, st, nz, count, W, C, perm, bij, d_cost);
+#define GE_MODE(NT_, TP_)                                                                                 \
+    if (java) GE_GO(NT_, true, false, false)                                                              \
+    else if (c.update == GE_UPDATE_STORE) GE_GO(NT_, false, false, TP_)                                   \
+    else GE_GO(NT_, false, true, TP_)
+    switch (nt) {
+        case 1: if (ctx->D4 >= 128) { GE_MODE(1, true) } else { GE_MODE(1, false) } break;
+        case 2: GE_MODE(2, true) break;
+        case 3: GE_MODE(3, true) break;
+        case 4: GE_MODE(4, true) break;
+        case 6: GE_MODE(6, true) break;
+        case 8: GE_MODE(8, true) break;
+        default: ctx->err = "dim too large (max 1024)"; return GE_ERR_INVALID;
+    }
+#undef GE_MODE
+#undef GE_GO
+    GE_CUDA(cudaGetLastError());
+    return GE_OK;
 }
 
 void ge_free_store(ge_ctx* ctx) {

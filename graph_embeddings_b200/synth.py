@@ -226,6 +226,35 @@ def synthetic_coo(V: int, nnz: int, seed: int = 6, s: float = 1.0):
     return i, j, x
 
 
+def synthetic_coo_torch(V: int, nnz: int, row_first: int, row_count: int, seed: int = 6, device="cuda"):
+    """C5-style direct COO for ONE rank of the block-rotation trainer, generated with torch on
+    `device`: rows Zipf(1)-distributed over the rank's own id range [row_first, row_first+row_count)
+    (hashed to decorrelate id and popularity), columns Zipf(1) over all V ids, X ~ U(1e-4, 0.2).
+    Returns host numpy arrays (ge_cooc_import takes host pointers)."""
+    import torch
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed * 1000003 + row_first)
+
+    def lsr(x, n):
+        return (x >> n) & ((1 << (64 - n)) - 1)
+
+    def mix(x):
+        x = (x ^ lsr(x, 30)) * (-4658895280553007687)
+        x = (x ^ lsr(x, 27)) * (-7723592293110705685)
+        return x ^ lsr(x, 31)
+
+    def zipf(n_ids, salt):
+        u = torch.rand(nnz, device=device, generator=gen, dtype=torch.float64)
+        r = torch.floor(torch.exp(u * float(np.log(n_ids)))).to(torch.int64) - 1
+        return lsr(mix(r + salt), 1) % n_ids
+
+    i = (row_first + zipf(row_count, seed)).to(torch.int32).cpu().numpy()
+    j = zipf(V, seed + 1).to(torch.int32).cpu().numpy()
+    x = (1e-4 + (0.2 - 1e-4) * torch.rand(nnz, device=device, generator=gen)).to(torch.float32).cpu().numpy()
+    return i, j, x
+
+
 def rmat_torch(V: int, E: int, seed: int, device="cuda", a=0.57, b=0.19, c=0.19, light_frac=0.1) -> CsrGraph:
     """Same construction as rmat() but generated with torch on `device` (bench-scale graphs:
     100 M edges in seconds).  The random stream differs from the numpy version; parity tests

@@ -13,7 +13,7 @@ opt = createOptimizer(c, b)
 B = 32 * dim + 44
 for _ in range(2):
     opt.epoch()
-for pf in [0, 1, 2, 4, 8, 16, 0, 2]:
+for pf in [int(x) for x in os.environ.get('PF_LIST', '0').split(',')]:
     os.environ["GE_PF_DIST"] = str(pf)
     ts = []
     for _ in range(3):
