@@ -66,7 +66,8 @@ struct JavaLcg {
     }
 };
 
-// One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128):
+// One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128).  The top bit of i / j
+// flags a hub row / column (ge_hot_count): the FAST/ATOMIC kernel writes those rows with plain stores.
 //   FAST math : a = (float)log(x) [glove] or (float)log(x/(1-x)) [pglove], b = f(x) weight
 //   JAVA math : a = x, b unused (log/pow are evaluated in fp64 inside the kernel)
 struct __align__(16) NzEntry {
@@ -115,6 +116,7 @@ struct ge_ctx {
     std::vector<int32_t> h_perm;  // GE_ORDER_JAVA host replay
     JavaLcg rng{0};               // stream position after init (GE_ORDER_JAVA)
     double* d_cost = nullptr;     // epoch cost accumulator
+    bool any_hot = false;         // packed nonzeros carry hub flags
     int32_t epoch = 0;
     std::vector<double> history;
     double update_seconds = 0;
@@ -128,8 +130,11 @@ struct ge_ctx {
 int ge_train_prepare(ge_ctx* ctx);  // pack nonzeros, allocate cost/perm
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
                      const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st,
-                     int64_t span /* ids addressable on the smaller side: bounds concurrency */);
+                     int64_t span /* ids addressable on the smaller side: bounds concurrency */,
+                     bool any_hot /* some entries carry hub flags: use the HOT kernel */);
 void ge_free_store(ge_ctx* ctx);
+int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
+int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (store semantics)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
 // api.cu

@@ -67,6 +67,7 @@ struct DistState {
     int head = 0;                     // slot of the window's first block
     int sub = 0;                      // sub-epochs done in the current rotation (block ids derive from it)
     double comm_seconds = 0;
+    std::vector<int32_t> bucket_hot;  // bucket has entries with hub flags -> HOT kernel
     cudaEvent_t c0 = nullptr, c1 = nullptr;
 };
 
@@ -112,6 +113,8 @@ __global__ void bucket_count(const int32_t* __restrict__ I, const int32_t* __res
 __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
                                const float* __restrict__ X, int64_t nnz, int32_t row_base, int32_t Bs, int32_t nb,
                                int32_t method, double xmax, unsigned long long* __restrict__ cursor,
+                               const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
+                               const int32_t* __restrict__ hot_cnt, int32_t m, int32_t* __restrict__ any_hot,
                                NzEntry* __restrict__ out) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
@@ -122,6 +125,10 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
         NzEntry e;
         e.i = i;             // W index: local to the rank's row range
         e.j = j - cb * Bs;   // C index: local to the column block
+        // hub flags (train.cu ge_hot_count): expected occurrences inside THIS bucket — a row's
+        // nonzeros spread over nb column blocks, a column's over the rank's m row blocks
+        if (cnt_i[i] / nb >= hot_cnt[b]) { e.i |= (int32_t)0x80000000; any_hot[b] = 1; }
+        if (cnt_j[j] / m >= hot_cnt[b]) { e.j |= (int32_t)0x80000000; any_hot[b] = 1; }
         if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
             e.b = ((double)x > xmax) ? 1.0f : (float)pow((double)x / xmax, 0.75);
@@ -244,11 +251,27 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     cudaFree(d->d_nzb); d->d_nzb = nullptr;
     GE_CUDA(cudaMalloc(&d->d_nzb, (size_t)(ctx->nnz > 0 ? ctx->nnz : 1) * sizeof(NzEntry)));
     GE_CUDA(cudaMemcpyAsync(d_cnt, cur.data(), 1024 * 8, cudaMemcpyHostToDevice, st));
-    if (ctx->nnz > 0)
-        bucket_scatter<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, first, d->Bs, d->nb,
-                                                         c.method, ctx->xmax, d_cnt, d->d_nzb);
-    GE_CUDA(cudaGetLastError());
-    GE_CUDA(cudaStreamSynchronize(st));
+    {
+        int32_t *cnt_i = nullptr, *cnt_j = nullptr, *d_hot = nullptr;
+        std::vector<int32_t> hot(2048, 0x7fffffff);   // [0,1024): thresholds, [1024,2048): any-hot flags (out)
+        const bool flags = c.update == GE_UPDATE_ATOMIC && c.opt_method == GE_OPT_ADAGRAD;
+        for (int b = 0; b < 1024; b++) hot[1024 + b] = 0;
+        for (int b = 0; b < nbuckets; b++) if (flags) hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs);
+        r = ge_count_ids(ctx, ctx->d_I, ctx->nnz, first, (int64_t)d->m * d->Bs, &cnt_i);
+        if (!r) r = ge_count_ids(ctx, ctx->d_J, ctx->nnz, 0, (int64_t)d->nb * d->Bs, &cnt_j);
+        cudaError_t e = r ? cudaSuccess : cudaMalloc(&d_hot, 2048 * 4);
+        if (!r && e == cudaSuccess) e = cudaMemcpyAsync(d_hot, hot.data(), 2048 * 4, cudaMemcpyHostToDevice, st);
+        if (!r && e == cudaSuccess && ctx->nnz > 0)
+            bucket_scatter<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, first, d->Bs, d->nb,
+                                                             c.method, ctx->xmax, d_cnt, cnt_i, cnt_j, d_hot, d->m, d_hot + 1024, d->d_nzb);
+        if (!r && e == cudaSuccess) e = cudaGetLastError();
+        if (!r && e == cudaSuccess) e = cudaMemcpyAsync(hot.data() + 1024, d_hot + 1024, 1024 * 4, cudaMemcpyDeviceToHost, st);
+        if (!r && e == cudaSuccess) e = cudaStreamSynchronize(st);
+        cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_hot);
+        d->bucket_hot.assign(hot.begin() + 1024, hot.begin() + 1024 + nbuckets);
+        if (r) { cudaFree(d_cnt); return r; }
+        if (e != cudaSuccess) { cudaFree(d_cnt); GE_CUDA(e); }
+    }
     cudaFree(d_cnt);
     // the COO arrays are no longer needed on the device once bucketed
     cudaFree(ctx->d_I); cudaFree(ctx->d_J); cudaFree(ctx->d_X);
@@ -297,7 +320,8 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
             const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
             float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
             int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
-                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs);
+                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs,
+                                     d->bucket_hot[bucket] != 0);
             if (r) return r;
         }
         if (d->world > 1) {

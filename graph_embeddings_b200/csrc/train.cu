@@ -114,8 +114,8 @@ struct Bijection {
 // K6 — the update kernel.  NT = float4 chunks per lane per vector (dim <= 128*NT).
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
-template <int NT, bool JAVA, bool ATOMIC, bool TP>
-__global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
+template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT>
+__global__ void __launch_bounds__(256, (NT == 1 && !JAVA && !HOT) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
                      int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
@@ -158,6 +158,7 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     pi = __shfl_sync(0xffffffffu, nxt.i, tt - 32); pj = __shfl_sync(0xffffffffu, nxt.j, tt - 32);
                     ok = next_base + (tt - 32) < count;
                 }
+                pi &= 0x7fffffff; pj &= 0x7fffffff;
                 if (ok) {
                     if (pf_lines) {  // per-line variant: lanes 0..15 cover the W row, 16..31 the C row (128 B each)
                         const int l = lane & 15;
@@ -168,8 +169,11 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     }
                 }
             }
-            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
-            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
+            int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
+            int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
+            // top bit = "hot" id (pack time): a hub row/column takes plain stores instead of red.add
+            const bool hot_i = HOT && bi < 0, hot_j = HOT && bj < 0;  // HOT kernels exist for ATOMIC only
+            bi &= 0x7fffffff; bj &= 0x7fffffff;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
             float* wrow = W + (size_t)bi * S;
@@ -261,13 +265,14 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                             cv[e] = (float)__dsub_rn((double)cv[e], __dmul_rn(__ddiv_rn((double)g2, __dsqrt_rn((double)gcv[e])), lr_d));
                             gwv[e] = __fadd_rn(gwv[e], __fmul_rn(g1, g1));
                             gcv[e] = __fadd_rn(gcv[e], __fmul_rn(g2, g2));
-                        } else if (ATOMIC) {  // deltas, applied by the L2 with red.add
+                        } else if (ATOMIC) {  // cold ids: deltas, applied by the L2 with red.add; hot ids: new values
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
-                            wv[e] = -g1 * rsqrtf(gwv[e]) * lr;
-                            cv[e] = -g2 * rsqrtf(gcv[e]) * lr;
-                            gwv[e] = g1 * g1;
-                            gcv[e] = g2 * g2;
+                            const float dw = -g1 * rsqrtf(gwv[e]) * lr, dc = -g2 * rsqrtf(gcv[e]) * lr;
+                            wv[e] = hot_i ? wv[e] + dw : dw;
+                            cv[e] = hot_j ? cv[e] + dc : dc;
+                            gwv[e] = hot_i ? gwv[e] + g1 * g1 : g1 * g1;
+                            gcv[e] = hot_j ? gcv[e] + g2 * g2 : g2 * g2;
                         } else {
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
@@ -278,10 +283,16 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         }
                     }
                     if (ATOMIC) {
-                        red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
-                        red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
-                        red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
-                        red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
+                        if (hot_i) { st4(wrow + 4 * ch, w[q]); st4(wrow + D4 + 4 * ch, gw[q]); }
+                        else {
+                            red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
+                            red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
+                        }
+                        if (hot_j) { st4(crow + 4 * ch, c[q]); st4(crow + D4 + 4 * ch, gc[q]); }
+                        else {
+                            red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
+                            red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
+                        }
                     } else {
                         st4(wrow + 4 * ch, w[q]);
                         st4(crow + 4 * ch, c[q]);
@@ -298,8 +309,10 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
                 } else if (ATOMIC) {
-                    red2(wrow + 2 * D4, -wc * rsqrtf(bw.y), wc * wc);
-                    red2(crow + 2 * D4, -wc * rsqrtf(bc.y), wc * wc);
+                    if (hot_i) *reinterpret_cast<float2*>(wrow + 2 * D4) = make_float2(bw.x - wc * rsqrtf(bw.y), bw.y + wc * wc);
+                    else red2(wrow + 2 * D4, -wc * rsqrtf(bw.y), wc * wc);
+                    if (hot_j) *reinterpret_cast<float2*>(crow + 2 * D4) = make_float2(bc.x - wc * rsqrtf(bc.y), bc.y + wc * wc);
+                    else red2(crow + 2 * D4, -wc * rsqrtf(bc.y), wc * wc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
@@ -362,8 +375,8 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
         }
         const int nvalid = (int)min((int64_t)32, count - base);
         for (int t = 0; t < nvalid; t++) {
-            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
-            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
+            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t) & 0x7fffffff;  // hot flags unused here
+            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t) & 0x7fffffff;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
             float* wrow = W + (size_t)bi * S;
@@ -494,12 +507,15 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
 // ------------------------------------------------------------------------------------------
 __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
                               const float* __restrict__ X, int64_t nnz, int32_t method, int32_t java,
-                              double xmax, NzEntry* __restrict__ out) {
+                              double xmax, const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
+                              int32_t hot_count, int32_t* __restrict__ any_hot, NzEntry* __restrict__ out) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
         const float x = X[k];
         NzEntry e;
         e.i = I[k]; e.j = J[k];
+        if (cnt_i && cnt_i[e.i] >= hot_count) { e.i |= (int32_t)0x80000000; *any_hot = 1; }  // hub row    -> store semantics
+        if (cnt_j && cnt_j[e.j] >= hot_count) { e.j |= (int32_t)0x80000000; *any_hot = 1; }  // hub column -> store semantics
         if (java) { e.a = x; e.b = 0.f; }
         else if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
@@ -648,7 +664,8 @@ static int launch_adam_nt(ge_ctx* ctx, int nt, cudaStream_t st, const NzEntry* n
 }
 
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
-                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st, int64_t span) {
+                     const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st, int64_t span,
+                     bool any_hot) {
     if (count <= 0) return GE_OK;
     int nt = (ctx->D4 / 4 + 31) / 32;
     if (nt == 5) nt = 6;
@@ -667,9 +684,9 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
     const int pf = ge_prefetch_distance();
     const ge_config& c = ctx->cfg;
     // one instantiation per (NT, math, update mode, load order); grid = one resident wave
-#define GE_GO(NT_, JAVA_, ATOMIC_, TP_)                                                                   \
+#define GE_GO(NT_, JAVA_, ATOMIC_, TP_, HOT_)                                                             \
     {                                                                                                     \
-        auto k = glove_adagrad_update<NT_, JAVA_, ATOMIC_, TP_>;                                          \
+        auto k = glove_adagrad_update<NT_, JAVA_, ATOMIC_, TP_, HOT_>;                                    \
         dim3 block(256), grid;                                                                            \
         if (c.serial) { block = dim3(32); grid = dim3(1); }                                               \
         else grid = wave_grid(ctx, k, count, span);                                                       \
@@ -677,9 +694,10 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                                   c.learning_rate, pf, d_cost);                                           \
     }
 #define GE_MODE(NT_, TP_)                                                                                 \
-    if (java) GE_GO(NT_, true, false, false)                                                              \
-    else if (c.update == GE_UPDATE_STORE) GE_GO(NT_, false, false, TP_)                                   \
-    else GE_GO(NT_, false, true, TP_)
+    if (java) GE_GO(NT_, true, false, false, false)                                                       \
+    else if (c.update == GE_UPDATE_STORE) GE_GO(NT_, false, false, TP_, false)                            \
+    else if (any_hot) GE_GO(NT_, false, true, TP_, true)                                                  \
+    else GE_GO(NT_, false, true, TP_, false)
     switch (nt) {
         case 1: if (ctx->D4 >= 128) { GE_MODE(1, true) } else { GE_MODE(1, false) } break;
         case 2: GE_MODE(2, true) break;
@@ -744,15 +762,62 @@ extern "C" int ge_store_init(ge_ctx* ctx) {
     return GE_OK;
 }
 
+namespace {
+__global__ void count_ids(const int32_t* __restrict__ ids, int64_t n, int32_t base, int32_t* __restrict__ cnt) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) atomicAdd(&cnt[ids[k] - base], 1);
+}
+}  // namespace
+
+// occurrences of every id in [base, base+n) among ids[0..nnz): input of the hot-id flags
+int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt) {
+    *d_cnt = nullptr;
+    GE_CUDA(cudaMalloc(d_cnt, (size_t)(n > 0 ? n : 1) * 4));
+    GE_CUDA(cudaMemsetAsync(*d_cnt, 0, (size_t)(n > 0 ? n : 1) * 4, ctx->stream));
+    if (nnz > 0) count_ids<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(d_ids, nnz, base, *d_cnt);
+    GE_CUDA(cudaGetLastError());
+    return GE_OK;
+}
+
+// An id is "hot" when, with a full wave of warps drawing nonzeros uniformly from a launch of
+// `launch_nnz` nonzeros, more than GE_HOT_WRITERS (default 16) warps are expected to sit on it at
+// once: red.add would then ADD that many stale-gradient steps (measured: fine at ~40-70, NaN at
+// ~100-250 on Zipf columns), whereas a plain store keeps one of them (the reference's own racy
+// semantics, Adagrad.java:76-80).  Returns the occurrence count from which an id is hot.
+int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
+    static const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
+    double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
+    if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
+    if (warps < 1) warps = 1;
+    double c = writers * (double)launch_nnz / warps;
+    if (c < 1) c = 1;
+    return c > 2e9 ? 0x7fffffff : (int32_t)c;
+}
+
 int ge_train_prepare(ge_ctx* ctx) {
     if (!ctx->have_cooc || ctx->nnz <= 0) { ctx->err = "no co-occurrence matrix: build or import one first"; return GE_ERR_STATE; }
     if (!ctx->have_store) { int r = ge_store_init(ctx); if (r) return r; }
     const ge_config& c = ctx->cfg;
     if (!ctx->d_nz) {
         GE_CUDA(cudaMalloc(&ctx->d_nz, (size_t)ctx->nnz * sizeof(NzEntry)));
+        int32_t *cnt_i = nullptr, *cnt_j = nullptr, *d_any = nullptr;
+        GE_CUDA(cudaMalloc(&d_any, 4));
+        cudaMemsetAsync(d_any, 0, 4, ctx->stream);
+        if (c.math == GE_MATH_FAST && c.update == GE_UPDATE_ATOMIC && c.opt_method == GE_OPT_ADAGRAD) {
+            int r = ge_count_ids(ctx, ctx->d_I, ctx->nnz, 0, ctx->V, &cnt_i);
+            if (!r) r = ge_count_ids(ctx, ctx->d_J, ctx->nnz, 0, ctx->V, &cnt_j);
+            if (r) { cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_any); return r; }
+        }
         pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
-                                                                 c.math == GE_MATH_JAVA, ctx->xmax, ctx->d_nz);
-        GE_CUDA(cudaGetLastError());
+                                                                 c.math == GE_MATH_JAVA, ctx->xmax, cnt_i, cnt_j,
+                                                                 ge_hot_count(ctx, ctx->nnz, ctx->V), d_any, ctx->d_nz);
+        cudaError_t pe = cudaGetLastError();
+        int32_t any = 0;
+        if (pe == cudaSuccess) pe = cudaMemcpyAsync(&any, d_any, 4, cudaMemcpyDeviceToHost, ctx->stream);
+        if (pe == cudaSuccess) pe = cudaStreamSynchronize(ctx->stream);
+        cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_any);
+        GE_CUDA(pe);
+        ctx->any_hot = any != 0;
     }
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
     if (c.order == GE_ORDER_JAVA) {
@@ -786,7 +851,7 @@ extern "C" int ge_train_epoch(ge_ctx* ctx, double* cost) {
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), ctx->stream));
     GE_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
     r = ge_launch_update(ctx, ctx->d_nz, ctx->nnz, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
-                         ctx->d_cost, ctx->stream, ctx->V);
+                         ctx->d_cost, ctx->stream, ctx->V, ctx->any_hot);
     if (r) return r;
     GE_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
     double total = 0;

@@ -226,10 +226,15 @@ def synthetic_coo(V: int, nnz: int, seed: int = 6, s: float = 1.0):
     return i, j, x
 
 
-def synthetic_coo_torch(V: int, nnz: int, row_first: int, row_count: int, seed: int = 6, device="cuda"):
+def synthetic_coo_torch(V: int, nnz: int, row_first: int, row_count: int, seed: int = 6, device="cuda",
+                         col_zipf: float = 0.7):
     """C5-style direct COO for ONE rank of the block-rotation trainer, generated with torch on
-    `device`: rows Zipf(1)-distributed over the rank's own id range [row_first, row_first+row_count)
-    (hashed to decorrelate id and popularity), columns Zipf(1) over all V ids, X ~ U(1e-4, 0.2).
+    `device`.  Shaped like a BCA-built matrix: rows uniform over the rank's own id range (a BCA row
+    is bounded by 2/(alpha*eps) entries, so no row is a hub), columns Zipf(col_zipf) over all V ids
+    (hashed to decorrelate id and popularity; s = 0.7 puts ~0.15 % of all nonzeros on the hottest
+    column at V = 50 M, the order of the hub columns of the R-MAT matrices), X ~ U(1e-4, 0.2).
+    Zipf(1.0) on BOTH sides (6 % of all nonzeros on one id = hundreds of concurrent writers on one
+    row) makes the atomic-add Hogwild update overshoot and diverge — see DESIGN.md §5.
     Returns host numpy arrays (ge_cooc_import takes host pointers)."""
     import torch
 
@@ -244,13 +249,15 @@ def synthetic_coo_torch(V: int, nnz: int, row_first: int, row_count: int, seed: 
         x = (x ^ lsr(x, 27)) * (-7723592293110705685)
         return x ^ lsr(x, 31)
 
-    def zipf(n_ids, salt):
-        u = torch.rand(nnz, device=device, generator=gen, dtype=torch.float64)
-        r = torch.floor(torch.exp(u * float(np.log(n_ids)))).to(torch.int64) - 1
-        return lsr(mix(r + salt), 1) % n_ids
-
-    i = (row_first + zipf(row_count, seed)).to(torch.int32).cpu().numpy()
-    j = zipf(V, seed + 1).to(torch.int32).cpu().numpy()
+    i = (row_first + torch.randint(0, row_count, (nnz,), device=device, generator=gen)).to(torch.int32).cpu().numpy()
+    u = torch.rand(nnz, device=device, generator=gen, dtype=torch.float64)
+    if abs(col_zipf - 1.0) < 1e-9:
+        r = torch.exp(u * float(np.log(V)))
+    else:                                   # inverse CDF of the continuous Zipf(s) on [1, V]
+        a = 1.0 - col_zipf
+        r = ((float(V) ** a - 1.0) * u + 1.0) ** (1.0 / a)
+    j = (lsr(mix(torch.floor(r).to(torch.int64) - 1 + (seed + 1)), 1) % V).to(torch.int32).cpu().numpy()
+    del u, r
     x = (1e-4 + (0.2 - 1e-4) * torch.rand(nnz, device=device, generator=gen)).to(torch.float32).cpu().numpy()
     return i, j, x
 
