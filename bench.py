@@ -251,7 +251,12 @@ def run_single(args):
 
 
 def main():
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
+    # stdout carries exactly one JSON line: whatever native libraries print on fd 1 (NCCL's version
+    # banner, ...) is sent to stderr; Python's own stdout keeps the real descriptor
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)

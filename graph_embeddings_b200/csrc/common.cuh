@@ -131,7 +131,8 @@ int ge_train_prepare(ge_ctx* ctx);  // pack nonzeros, allocate cost/perm
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
                      const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st,
                      int64_t span /* ids addressable on the smaller side: bounds concurrency */,
-                     bool any_hot /* some entries carry hub flags: use the HOT kernel */);
+                     bool any_hot /* some entries carry hub flags: use the HOT kernel */,
+                     unsigned long long* queue /* zeroed device counter: dynamic batch claiming; nullptr = static */);
 void ge_free_store(ge_ctx* ctx);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (store semantics)

@@ -64,6 +64,12 @@ struct DistState {
     std::vector<int64_t> bucket_off;  // m*nb + 1 offsets into d_nzb, bucket = local_rowblock*nb + colblock
     NzEntry* d_nzb = nullptr;         // bucketed nonzeros, block-local indices
     float* d_Cring = nullptr;         // (m+1) slots x Bs rows x S floats (m slots when world == 1)
+    int P = 1;                        // parts per column block (2 when world > 1: the rotation is pipelined
+                                      // half a block at a time behind the compute), Hs = rows in part 0
+    int32_t Hs = 0;
+    cudaStream_t cs = nullptr;        // high-priority stream the ncclSend/ncclRecv pairs run on
+    cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_recv[2] = {nullptr, nullptr};
+    unsigned long long* d_queue = nullptr;  // one batch counter per update launch of an epoch
     int head = 0;                     // slot of the window's first block
     int sub = 0;                      // sub-epochs done in the current rotation (block ids derive from it)
     double comm_seconds = 0;
@@ -76,6 +82,9 @@ void ge_dist_free(ge_ctx* ctx) {
     if (!d) return;
     cudaFree(d->d_nzb);
     cudaFree(d->d_Cring);
+    cudaFree(d->d_queue);
+    for (int p = 0; p < 2; p++) { if (d->ev_done[p]) cudaEventDestroy(d->ev_done[p]); if (d->ev_recv[p]) cudaEventDestroy(d->ev_recv[p]); }
+    if (d->cs) cudaStreamDestroy(d->cs);
     if (d->c0) cudaEventDestroy(d->c0);
     if (d->c1) cudaEventDestroy(d->c1);
     if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
@@ -95,13 +104,16 @@ namespace {
     } while (0)
 
 __global__ void bucket_count(const int32_t* __restrict__ I, const int32_t* __restrict__ J, int64_t nnz,
-                             int32_t row_base, int32_t Bs, int32_t nb, unsigned long long* __restrict__ cnt) {
+                             int32_t row_base, int32_t Bs, int32_t nb, int32_t P, int32_t Hs,
+                             unsigned long long* __restrict__ cnt) {
     __shared__ unsigned int local[1024];
     for (int k = threadIdx.x; k < 1024; k += blockDim.x) local[k] = 0;
     __syncthreads();
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
-        const int b = ((I[k] - row_base) / Bs) * nb + J[k] / Bs;
+        const int cb = J[k] / Bs;
+        const int part = (P > 1 && J[k] - cb * Bs >= Hs) ? 1 : 0;
+        const int b = (((I[k] - row_base) / Bs) * nb + cb) * P + part;
         atomicAdd(&local[b], 1u);
     }
     __syncthreads();
@@ -112,7 +124,7 @@ __global__ void bucket_count(const int32_t* __restrict__ I, const int32_t* __res
 // scatter into buckets with block-local indices; warp-aggregated cursor claims
 __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
                                const float* __restrict__ X, int64_t nnz, int32_t row_base, int32_t Bs, int32_t nb,
-                               int32_t method, double xmax, unsigned long long* __restrict__ cursor,
+                               int32_t P, int32_t Hs, int32_t method, double xmax, unsigned long long* __restrict__ cursor,
                                const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
                                const int32_t* __restrict__ hot_cnt, int32_t m, int32_t* __restrict__ any_hot,
                                NzEntry* __restrict__ out) {
@@ -120,14 +132,15 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
         const int32_t i = I[k] - row_base, j = J[k];
         const int cb = j / Bs;
-        const int b = (i / Bs) * nb + cb;
+        const int part = (P > 1 && j - cb * Bs >= Hs) ? 1 : 0;
+        const int b = ((i / Bs) * nb + cb) * P + part;
         const float x = X[k];
         NzEntry e;
         e.i = i;             // W index: local to the rank's row range
         e.j = j - cb * Bs;   // C index: local to the column block
         // hub flags (train.cu ge_hot_count): expected occurrences inside THIS bucket — a row's
         // nonzeros spread over nb column blocks, a column's over the rank's m row blocks
-        if (cnt_i[i] / nb >= hot_cnt[b]) { e.i |= (int32_t)0x80000000; any_hot[b] = 1; }
+        if (cnt_i[i] / (nb * P) >= hot_cnt[b]) { e.i |= (int32_t)0x80000000; any_hot[b] = 1; }
         if (cnt_j[j] / m >= hot_cnt[b]) { e.j |= (int32_t)0x80000000; any_hot[b] = 1; }
         if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
@@ -177,7 +190,16 @@ extern "C" int ge_dist_init(ge_ctx* ctx, int32_t rank, int32_t world, const void
         if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
         NcclId id;
         memcpy(&id, id128, GE_NCCL_ID_BYTES);
+        // the rotation is point-to-point only: give send/recv enough channels to fill NVLink
+        setenv("NCCL_MIN_P2P_NCHANNELS", "8", 0);
         GE_NCCL(g_nccl.CommInitRank(&d->comm, world, id, rank));
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        GE_CUDA(cudaStreamCreateWithPriority(&d->cs, cudaStreamNonBlocking, hi));
+        for (int p = 0; p < 2; p++) {
+            GE_CUDA(cudaEventCreateWithFlags(&d->ev_done[p], cudaEventDisableTiming));
+            GE_CUDA(cudaEventCreateWithFlags(&d->ev_recv[p], cudaEventDisableTiming));
+        }
     }
     GE_CUDA(cudaEventCreate(&d->c0));
     GE_CUDA(cudaEventCreate(&d->c1));
@@ -215,6 +237,13 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     }
     d->nb = nblocks; d->m = nblocks / d->world;
     d->Bs = (ctx->V + nblocks - 1) / nblocks;
+    // GE_DIST_PIPE=1: half-block rotation on a second stream behind the compute (measured on 2 B200s:
+    // C5 -5 %, C4 +6 % time: NCCL's copy CTAs cannot get SM slots beside the persistent update wave, so it
+    // stays opt-in; default = whole-block rotation on the compute stream)
+    static const bool pipe = getenv("GE_DIST_PIPE") && atoi(getenv("GE_DIST_PIPE")) == 1;
+    d->P = (d->world > 1 && pipe) ? 2 : 1;
+    d->Hs = d->P > 1 ? (d->Bs + 1) / 2 : d->Bs;
+    if (d->m * d->nb * d->P > 1024) { ctx->err = "too many buckets (nblocks^2 / world * 2 must be <= 1024)"; return GE_ERR_INVALID; }
     d->row_base = first; d->row_cnt = count;
 
     // global max (f(x) weight uses it, GloveCost.java:19) and global nnz (cost normaliser)
@@ -236,12 +265,12 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     d->nnz_global = hn;
 
     // ---- K7: bucket the local nonzeros by (row-block, col-block)
-    const int nbuckets = d->m * d->nb;
+    const int nbuckets = d->m * d->nb * d->P;
     unsigned long long* d_cnt = nullptr;
     GE_CUDA(cudaMalloc(&d_cnt, 1024 * 8));
     GE_CUDA(cudaMemsetAsync(d_cnt, 0, 1024 * 8, st));
     if (ctx->nnz > 0)
-        bucket_count<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->nnz, first, d->Bs, d->nb, d_cnt);
+        bucket_count<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->nnz, first, d->Bs, d->nb, d->P, d->Hs, d_cnt);
     std::vector<unsigned long long> hc(1024);
     GE_CUDA(cudaMemcpyAsync(hc.data(), d_cnt, 1024 * 8, cudaMemcpyDeviceToHost, st));
     GE_CUDA(cudaStreamSynchronize(st));
@@ -263,7 +292,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         if (!r && e == cudaSuccess) e = cudaMemcpyAsync(d_hot, hot.data(), 2048 * 4, cudaMemcpyHostToDevice, st);
         if (!r && e == cudaSuccess && ctx->nnz > 0)
             bucket_scatter<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, first, d->Bs, d->nb,
-                                                             c.method, ctx->xmax, d_cnt, cnt_i, cnt_j, d_hot, d->m, d_hot + 1024, d->d_nzb);
+                                                             d->P, d->Hs, c.method, ctx->xmax, d_cnt, cnt_i, cnt_j, d_hot, d->m, d_hot + 1024, d->d_nzb);
         if (!r && e == cudaSuccess) e = cudaGetLastError();
         if (!r && e == cudaSuccess) e = cudaMemcpyAsync(hot.data() + 1024, d_hot + 1024, 1024 * 4, cudaMemcpyDeviceToHost, st);
         if (!r && e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -290,6 +319,8 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, count, first);
     if (r) return r;
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
+    cudaFree(d->d_queue); d->d_queue = nullptr;
+    GE_CUDA(cudaMalloc(&d->d_queue, (size_t)nbuckets * sizeof(unsigned long long)));
     d->head = 0; d->sub = 0;
     ctx->epoch = 0;
     ctx->history.clear();
@@ -310,23 +341,49 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), st));
     GE_CUDA(cudaEventRecord(ctx->ev0, st));
     float comm_ms = 0;
+    const int P = d->P;
+    const bool piped = d->world > 1 && P > 1;
+    if (piped) GE_CUDA(cudaMemsetAsync(d->d_queue, 0, (size_t)d->m * d->nb * P * sizeof(unsigned long long), st));
+    // byte ranges of the P parts of a block slab (part 0 = rows [0, Hs), part 1 = rows [Hs, Bs))
+    const size_t part_off[2] = {0, (size_t)d->Hs * ctx->S};
+    const size_t part_len[2] = {(size_t)d->Hs * ctx->S, (size_t)(d->Bs - d->Hs) * ctx->S};
+    const int to = (d->rank + d->world - 1) % d->world, from = (d->rank + 1) % d->world;
     for (int s = 0; s < d->nb; s++) {
-        // window of C blocks held now: block (rank*m + s + k) mod nb sits in slot (head + k) mod slots
+        // window of C blocks held now: block (rank*m + s + k) mod nb sits in slot (head + k) mod slots.
+        // Pipelined rotation (world > 1): the window's FIRST block is updated first, part by part; as
+        // soon as a part is done it leaves for rank-1 on the copy stream while the next part / the
+        // other window blocks are being updated, and the matching part of the block arriving from
+        // rank+1 lands in the spare slot.  That block is the window's LAST one in the next sub-epoch,
+        // whose updates wait on the part's arrival only.
         for (int k = 0; k < d->m; k++) {
             const int cb = (d->rank * d->m + s + k) % d->nb;
-            // virtual rank v = rank*m + k' processes column block (v + s) mod nb  =>  k' = k
-            const int lrb = k;
-            const int bucket = lrb * d->nb + cb;
-            const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
+            const int lrb = k;  // virtual rank v = rank*m + k processes column block (v + s) mod nb
             float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
-            int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
-                                     ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs,
-                                     d->bucket_hot[bucket] != 0);
-            if (r) return r;
+            for (int p = 0; p < P; p++) {
+                const int bucket = (lrb * d->nb + cb) * P + p;
+                const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
+                if (piped && k == d->m - 1 && s > 0) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));
+                int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
+                                         ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs,
+                                         d->bucket_hot[bucket] != 0, piped ? d->d_queue + bucket : nullptr);
+                if (r) return r;
+                if (piped && k == 0) {
+                    float* sendp = d->d_Cring + (size_t)d->head * slab + part_off[p];
+                    float* recvp = d->d_Cring + (size_t)((d->head + d->m) % slots) * slab + part_off[p];
+                    GE_CUDA(cudaEventRecord(d->ev_done[p], st));
+                    GE_CUDA(cudaStreamWaitEvent(d->cs, d->ev_done[p], 0));
+                    const bool timed = s == d->nb - 1 && p == P - 1;
+                    if (timed) cudaEventRecord(d->c0, d->cs);
+                    GE_NCCL(g_nccl.GroupStart());
+                    GE_NCCL(g_nccl.Send(sendp, part_len[p] * sizeof(float), NCCL_UINT8, to, d->comm, d->cs));
+                    GE_NCCL(g_nccl.Recv(recvp, part_len[p] * sizeof(float), NCCL_UINT8, from, d->comm, d->cs));
+                    GE_NCCL(g_nccl.GroupEnd());
+                    if (timed) cudaEventRecord(d->c1, d->cs);
+                    GE_CUDA(cudaEventRecord(d->ev_recv[p], d->cs));
+                }
+            }
         }
-        if (d->world > 1) {
-            // hand the window's first block to rank-1, receive a new last block from rank+1
-            const int to = (d->rank + d->world - 1) % d->world, from = (d->rank + 1) % d->world;
+        if (d->world > 1 && !piped) {  // GE_DIST_PIPE=0: whole-block rotation on the compute stream
             float* sendp = d->d_Cring + (size_t)d->head * slab;
             float* recvp = d->d_Cring + (size_t)((d->head + d->m) % slots) * slab;
             cudaEventRecord(d->c0, st);
@@ -335,12 +392,10 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
             GE_NCCL(g_nccl.Recv(recvp, slab * sizeof(float), NCCL_UINT8, from, d->comm, st));
             GE_NCCL(g_nccl.GroupEnd());
             cudaEventRecord(d->c1, st);
-            d->head = (d->head + 1) % slots;
-        } else {
-            // one GPU holds every block: rotation is a pointer shift of the window
-            d->head = (d->head + 1) % slots;
         }
+        d->head = (d->head + 1) % slots;  // one GPU: the rotation is this pointer shift alone
     }
+    if (piped) for (int p = 0; p < P; p++) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));  // every block home
     if (d->world == 1) d->head = (d->head + slots - (d->nb % slots)) % slots;  // nb shifts of an nb-ring: identity
     GE_CUDA(cudaEventRecord(ctx->ev1, st));
     double total = 0;
@@ -350,7 +405,7 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->update_seconds += ms * 1e-3;
-    if (d->world > 1) { cudaEventElapsedTime(&comm_ms, d->c0, d->c1); d->comm_seconds += comm_ms * 1e-3 * d->nb; }
+    if (d->world > 1) { cudaEventElapsedTime(&comm_ms, d->c0, d->c1); d->comm_seconds += comm_ms * 1e-3 * d->nb * d->P; }
     const double local = total / (double)d->nnz_global;
     ctx->history.push_back(local);
     ctx->epoch++;
@@ -390,7 +445,7 @@ extern "C" int ge_dist_stats(ge_ctx* ctx, int64_t* bucket_nnz, int32_t cap, doub
     if (!ctx || !ctx->dist) return GE_ERR_STATE;
     DistState* d = ctx->dist;
     const int n = d->m * d->nb;
-    if (bucket_nnz) for (int b = 0; b < n && b < cap; b++) bucket_nnz[b] = d->bucket_off[b + 1] - d->bucket_off[b];
+    if (bucket_nnz) for (int b = 0; b < n && b < cap; b++) bucket_nnz[b] = d->bucket_off[(size_t)(b + 1) * d->P] - d->bucket_off[(size_t)b * d->P];
     if (comm_seconds) *comm_seconds = d->comm_seconds;
     if (nnz_global) *nnz_global = d->nnz_global;
     return n;

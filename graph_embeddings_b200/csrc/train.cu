@@ -114,12 +114,12 @@ struct Bijection {
 // K6 — the update kernel.  NT = float4 chunks per lane per vector (dim <= 128*NT).
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
-template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT>
-__global__ void __launch_bounds__(256, (NT == 1 && !JAVA && !HOT) ? 4 : 1)
+template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT, bool DYN>
+__global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? (HOT ? 3 : 4) : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
                      int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
-                     double* __restrict__ cost_out) {
+                     unsigned long long* __restrict__ queue, double* __restrict__ cost_out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -141,9 +141,27 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
     constexpr bool two_phase = TP;  // launcher: D4 >= 128 (rows at least one warp of float4 wide)
     const bool pf_lines = pf >= 100;  // GE_PF_DIST = 100 + distance selects prefetch.global.L2 per line
     if (pf_lines) pf -= 100;
-    NzEntry mine = fetch(warp * 32 + lane);
-    for (int64_t base = warp * 32; base < count; base += nwarps * 32) {
-        const int64_t next_base = base + nwarps * 32;
+    // Batches of 32 nonzeros.  !DYN: static grid-stride ownership (single-GPU epochs: one resident
+    // wave, every warp starts at once).  DYN: warps claim chunks of QCH batches from a global counter,
+    // so blocks that become resident late (the pipelined multi-GPU trainer runs NCCL copy kernels
+    // beside this one) simply claim less instead of stretching the tail.
+    constexpr int64_t QCH = 8;
+    auto claim = [&]() -> int64_t {  // first position of a freshly claimed chunk
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(queue, (unsigned long long)QCH);
+        return (int64_t)__shfl_sync(0xffffffffu, c, 0) * 32;
+    };
+    int64_t chunk_end = 0, next_chunk = 0;
+    int64_t base0 = warp * 32;
+    if (DYN) { base0 = claim(); chunk_end = base0 + QCH * 32; next_chunk = claim(); }
+    NzEntry mine = fetch(base0 + lane);
+    for (int64_t base = base0, next_base; base < count; base = next_base) {
+        if (DYN) {
+            next_base = base + 32;
+            if (next_base == chunk_end) { next_base = next_chunk; chunk_end = next_base + QCH * 32; next_chunk = claim(); }
+        } else {
+            next_base = base + nwarps * 32;
+        }
         const NzEntry nxt = fetch(next_base + lane);  // next batch: issued now, needed 32 nonzeros later
         const int nvalid = (int)min((int64_t)32, count - base);
         for (int t = 0; t < nvalid; t++) {
@@ -665,7 +683,7 @@ static int launch_adam_nt(ge_ctx* ctx, int nt, cudaStream_t st, const NzEntry* n
 
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
                      const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st, int64_t span,
-                     bool any_hot) {
+                     bool any_hot, unsigned long long* queue) {
     if (count <= 0) return GE_OK;
     int nt = (ctx->D4 / 4 + 31) / 32;
     if (nt == 5) nt = 6;
@@ -684,14 +702,19 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
     const int pf = ge_prefetch_distance();
     const ge_config& c = ctx->cfg;
     // one instantiation per (NT, math, update mode, load order); grid = one resident wave
-#define GE_GO(NT_, JAVA_, ATOMIC_, TP_, HOT_)                                                             \
+#define GE_GO2(NT_, JAVA_, ATOMIC_, TP_, HOT_, DYN_)                                                      \
     {                                                                                                     \
-        auto k = glove_adagrad_update<NT_, JAVA_, ATOMIC_, TP_, HOT_>;                                    \
+        auto k = glove_adagrad_update<NT_, JAVA_, ATOMIC_, TP_, HOT_, DYN_>;                              \
         dim3 block(256), grid;                                                                            \
         if (c.serial) { block = dim3(32); grid = dim3(1); }                                               \
         else grid = wave_grid(ctx, k, count, span);                                                       \
         k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax,       \
-                                  c.learning_rate, pf, d_cost);                                           \
+                                  c.learning_rate, pf, queue, d_cost);                                    \
+    }
+#define GE_GO(NT_, JAVA_, ATOMIC_, TP_, HOT_)                                                             \
+    {                                                                                                     \
+        if (queue && (ATOMIC_)) GE_GO2(NT_, JAVA_, ATOMIC_, TP_, HOT_, (ATOMIC_))                         \
+        else GE_GO2(NT_, JAVA_, ATOMIC_, TP_, HOT_, false)                                                \
     }
 #define GE_MODE(NT_, TP_)                                                                                 \
     if (java) GE_GO(NT_, true, false, false, false)                                                       \
@@ -709,6 +732,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
     }
 #undef GE_MODE
 #undef GE_GO
+#undef GE_GO2
     GE_CUDA(cudaGetLastError());
     return GE_OK;
 }
@@ -780,12 +804,12 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 }
 
 // An id is "hot" when, with a full wave of warps drawing nonzeros uniformly from a launch of
-// `launch_nnz` nonzeros, more than GE_HOT_WRITERS (default 16) warps are expected to sit on it at
+// `launch_nnz` nonzeros, more than GE_HOT_WRITERS (default 48) warps are expected to sit on it at
 // once: red.add would then ADD that many stale-gradient steps (measured: fine at ~40-70, NaN at
 // ~100-250 on Zipf columns), whereas a plain store keeps one of them (the reference's own racy
 // semantics, Adagrad.java:76-80).  Returns the occurrence count from which an id is hot.
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
-    static const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
+    static const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 48.0;
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
     if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
     if (warps < 1) warps = 1;
@@ -851,7 +875,7 @@ extern "C" int ge_train_epoch(ge_ctx* ctx, double* cost) {
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), ctx->stream));
     GE_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
     r = ge_launch_update(ctx, ctx->d_nz, ctx->nnz, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
-                         ctx->d_cost, ctx->stream, ctx->V, ctx->any_hot);
+                         ctx->d_cost, ctx->stream, ctx->V, ctx->any_hot, nullptr);
     if (r) return r;
     GE_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
     double total = 0;
