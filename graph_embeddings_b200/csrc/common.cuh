@@ -66,14 +66,27 @@ struct JavaLcg {
     }
 };
 
-// One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128).  The top bit of i / j
-// flags a hub row / column (ge_hot_count): the FAST/ATOMIC kernel writes those rows with plain stores.
+// One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128).  Bits 27..30 of i / j
+// carry the damping exponent k of a hub row / column (ge_damp_bits): the FAST/ATOMIC kernel scales
+// that side's delta by 2^(-k/2).  Ids therefore stay below 2^27 (GE_ID_MASK) — no restriction next
+// to the reference, whose int-indexed focus[] needs V * dim < 2^31.
 //   FAST math : a = (float)log(x) [glove] or (float)log(x/(1-x)) [pglove], b = f(x) weight
 //   JAVA math : a = x, b unused (log/pow are evaluated in fp64 inside the kernel)
 struct __align__(16) NzEntry {
     int32_t i, j;
     float a, b;
 };
+#define GE_ID_BITS 27
+#define GE_ID_MASK 0x07ffffff
+// Damping exponent of an id that occurs `cnt` times where `hot_count` occurrences mean
+// GE_HOT_WRITERS expected concurrent writers: the smallest k >= 1 with cnt * 2^(-k/2) < hot_count
+// (capped at 15), so that the scaled deltas of all concurrent writers add up to between
+// GE_HOT_WRITERS / sqrt(2) and GE_HOT_WRITERS full steps.  0 = not a hub.
+__host__ __device__ inline int32_t ge_damp_bits(int32_t cnt, int32_t hot_count) {
+    if (cnt < hot_count || hot_count <= 0) return 0;
+    const int32_t k = (int32_t)floorf(2.0f * log2f((float)cnt / (float)hot_count)) + 1;
+    return k > 15 ? 15 : k;
+}
 
 struct DistState;  // dist.cu
 
@@ -135,7 +148,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                      unsigned long long* queue /* zeroed device counter: dynamic batch claiming; nullptr = static */);
 void ge_free_store(ge_ctx* ctx);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
-int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (store semantics)
+int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (damped deltas)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
 // api.cu

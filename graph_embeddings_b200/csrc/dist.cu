@@ -140,8 +140,9 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
         e.j = j - cb * Bs;   // C index: local to the column block
         // hub flags (train.cu ge_hot_count): expected occurrences inside THIS bucket — a row's
         // nonzeros spread over nb column blocks, a column's over the rank's m row blocks
-        if (cnt_i[i] / (nb * P) >= hot_cnt[b]) { e.i |= (int32_t)0x80000000; any_hot[b] = 1; }
-        if (cnt_j[j] / m >= hot_cnt[b]) { e.j |= (int32_t)0x80000000; any_hot[b] = 1; }
+        const int32_t ki = ge_damp_bits(cnt_i[i] / (nb * P), hot_cnt[b]), kj = ge_damp_bits(cnt_j[j] / m, hot_cnt[b]);
+        if (ki) { e.i |= ki << GE_ID_BITS; any_hot[b] = 1; }
+        if (kj) { e.j |= kj << GE_ID_BITS; any_hot[b] = 1; }
         if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
             e.b = ((double)x > xmax) ? 1.0f : (float)pow((double)x / xmax, 0.75);
@@ -190,8 +191,6 @@ extern "C" int ge_dist_init(ge_ctx* ctx, int32_t rank, int32_t world, const void
         if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
         NcclId id;
         memcpy(&id, id128, GE_NCCL_ID_BYTES);
-        // the rotation is point-to-point only: give send/recv enough channels to fill NVLink
-        setenv("NCCL_MIN_P2P_NCHANNELS", "8", 0);
         GE_NCCL(g_nccl.CommInitRank(&d->comm, world, id, rank));
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);

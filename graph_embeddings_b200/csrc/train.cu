@@ -115,7 +115,7 @@ struct Bijection {
 // JAVA: reference promotion pattern (fp64 islands); otherwise f32 + rsqrt.
 // ------------------------------------------------------------------------------------------
 template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT, bool DYN>
-__global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? (HOT ? 3 : 4) : 1)
+__global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
                      int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
@@ -176,7 +176,7 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     pi = __shfl_sync(0xffffffffu, nxt.i, tt - 32); pj = __shfl_sync(0xffffffffu, nxt.j, tt - 32);
                     ok = next_base + (tt - 32) < count;
                 }
-                pi &= 0x7fffffff; pj &= 0x7fffffff;
+                pi &= GE_ID_MASK; pj &= GE_ID_MASK;
                 if (ok) {
                     if (pf_lines) {  // per-line variant: lanes 0..15 cover the W row, 16..31 the C row (128 B each)
                         const int l = lane & 15;
@@ -189,9 +189,14 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             }
             int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
             int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
-            // top bit = "hot" id (pack time): a hub row/column takes plain stores instead of red.add
-            const bool hot_i = HOT && bi < 0, hot_j = HOT && bj < 0;  // HOT kernels exist for ATOMIC only
-            bi &= 0x7fffffff; bj &= 0x7fffffff;
+            // bits 27..30 = damping exponent k of a hub id (pack time): its deltas are scaled by
+            // 2^(-k/2) so that the K stale steps the L2 adds up act like at most GE_HOT_WRITERS of them
+            float si = 1.f, sj = 1.f;
+            if (HOT) {  // HOT kernels exist for ATOMIC only
+                si = exp2f(-0.5f * (float)((bi >> GE_ID_BITS) & 15));
+                sj = exp2f(-0.5f * (float)((bj >> GE_ID_BITS) & 15));
+            }
+            bi &= GE_ID_MASK; bj &= GE_ID_MASK;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
             float* wrow = W + (size_t)bi * S;
@@ -283,14 +288,15 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                             cv[e] = (float)__dsub_rn((double)cv[e], __dmul_rn(__ddiv_rn((double)g2, __dsqrt_rn((double)gcv[e])), lr_d));
                             gwv[e] = __fadd_rn(gwv[e], __fmul_rn(g1, g1));
                             gcv[e] = __fadd_rn(gcv[e], __fmul_rn(g2, g2));
-                        } else if (ATOMIC) {  // cold ids: deltas, applied by the L2 with red.add; hot ids: new values
+                        } else if (ATOMIC) {  // deltas, applied by the L2 with red.add
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
-                            const float dw = -g1 * rsqrtf(gwv[e]) * lr, dc = -g2 * rsqrtf(gcv[e]) * lr;
-                            wv[e] = hot_i ? wv[e] + dw : dw;
-                            cv[e] = hot_j ? cv[e] + dc : dc;
-                            gwv[e] = hot_i ? gwv[e] + g1 * g1 : g1 * g1;
-                            gcv[e] = hot_j ? gcv[e] + g2 * g2 : g2 * g2;
+                            float dw = -g1 * rsqrtf(gwv[e]) * lr, dc = -g2 * rsqrtf(gcv[e]) * lr;
+                            if (HOT) { dw *= si; dc *= sj; }  // gradsq keeps the full g^2, as every reference update adds it
+                            wv[e] = dw;
+                            cv[e] = dc;
+                            gwv[e] = g1 * g1;
+                            gcv[e] = g2 * g2;
                         } else {
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
@@ -301,16 +307,10 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         }
                     }
                     if (ATOMIC) {
-                        if (hot_i) { st4(wrow + 4 * ch, w[q]); st4(wrow + D4 + 4 * ch, gw[q]); }
-                        else {
-                            red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
-                            red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
-                        }
-                        if (hot_j) { st4(crow + 4 * ch, c[q]); st4(crow + D4 + 4 * ch, gc[q]); }
-                        else {
-                            red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
-                            red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
-                        }
+                        red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
+                        red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
+                        red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
+                        red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
                     } else {
                         st4(wrow + 4 * ch, w[q]);
                         st4(crow + 4 * ch, c[q]);
@@ -327,10 +327,8 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
                 } else if (ATOMIC) {
-                    if (hot_i) *reinterpret_cast<float2*>(wrow + 2 * D4) = make_float2(bw.x - wc * rsqrtf(bw.y), bw.y + wc * wc);
-                    else red2(wrow + 2 * D4, -wc * rsqrtf(bw.y), wc * wc);
-                    if (hot_j) *reinterpret_cast<float2*>(crow + 2 * D4) = make_float2(bc.x - wc * rsqrtf(bc.y), bc.y + wc * wc);
-                    else red2(crow + 2 * D4, -wc * rsqrtf(bc.y), wc * wc);
+                    red2(wrow + 2 * D4, -wc * rsqrtf(bw.y) * si, wc * wc);
+                    red2(crow + 2 * D4, -wc * rsqrtf(bc.y) * sj, wc * wc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
@@ -393,8 +391,8 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
         }
         const int nvalid = (int)min((int64_t)32, count - base);
         for (int t = 0; t < nvalid; t++) {
-            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t) & 0x7fffffff;  // hot flags unused here
-            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t) & 0x7fffffff;
+            const int32_t bi = __shfl_sync(0xffffffffu, mine.i, t) & GE_ID_MASK;  // damping bits unused here
+            const int32_t bj = __shfl_sync(0xffffffffu, mine.j, t) & GE_ID_MASK;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
             float* wrow = W + (size_t)bi * S;
@@ -532,8 +530,8 @@ __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __re
         const float x = X[k];
         NzEntry e;
         e.i = I[k]; e.j = J[k];
-        if (cnt_i && cnt_i[e.i] >= hot_count) { e.i |= (int32_t)0x80000000; *any_hot = 1; }  // hub row    -> store semantics
-        if (cnt_j && cnt_j[e.j] >= hot_count) { e.j |= (int32_t)0x80000000; *any_hot = 1; }  // hub column -> store semantics
+        if (cnt_i) { const int32_t k = ge_damp_bits(cnt_i[e.i], hot_count); if (k) { e.i |= k << GE_ID_BITS; *any_hot = 1; } }  // hub row
+        if (cnt_j) { const int32_t k = ge_damp_bits(cnt_j[e.j], hot_count); if (k) { e.j |= k << GE_ID_BITS; *any_hot = 1; } }  // hub column
         if (java) { e.a = x; e.b = 0.f; }
         else if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
@@ -767,6 +765,7 @@ int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t ro
 extern "C" int ge_store_init(ge_ctx* ctx) {
     if (!ctx) return GE_ERR_INVALID;
     if (ctx->V <= 0) { ctx->err = "no vocabulary: set a graph or import a matrix first"; return GE_ERR_STATE; }
+    if (ctx->V > GE_ID_MASK) { ctx->err = "vocabulary must stay below 2^27 vertices (packed nonzero ids)"; return GE_ERR_INVALID; }
     const ge_config& c = ctx->cfg;
     cudaFree(ctx->d_W); cudaFree(ctx->d_C); ctx->d_W = ctx->d_C = nullptr;
     ge_store_geometry(ctx);

@@ -156,8 +156,9 @@ def test_errors():
 def test_hub_columns_do_not_diverge():
     """Zipf(1) columns: ~5 % of all nonzeros sit on one column, i.e. hundreds of concurrent warps
     on one C row.  With red.add every one of their stale-gradient steps would be ADDED (measured:
-    NaN in the first epoch); ids above ge_hot_count occurrences are flagged at pack time and take
-    plain stores instead (the reference's own last-writer-wins race, Adagrad.java:76-80).  Both the
+    NaN in the first epoch); ids above ge_hot_count occurrences get a damping exponent at pack time
+    and their deltas are scaled by 2^(-k/2), so the sum acts like at most GE_HOT_WRITERS steps (the
+    reference's own last-writer-wins race, Adagrad.java:76-80, loses those updates instead).  Both the
     single-GPU trainer and the 8x8 block schedule must stay finite and keep descending, close to
     the all-stores mode."""
     import torch
