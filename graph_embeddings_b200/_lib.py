@@ -31,6 +31,22 @@ class GeConfig(C.Structure):
                 ("device", C.c_int32), ("update", C.c_int32)]
 
 
+class GeSimGroup(C.Structure):
+    """ge_sim_group (include/graphemb.h)"""
+    _fields_ = [("method", C.c_int32), ("upper_triangle", C.c_int32), ("threshold", C.c_double),
+                ("smooth", C.c_double), ("distance", C.c_double), ("time_dir", C.c_int32),
+                ("n_items", C.c_int32), ("vert", C.c_void_p), ("string_id", C.c_void_p),
+                ("flags", C.c_void_p), ("prof_off", C.c_void_p), ("prof_key", C.c_void_p),
+                ("prof_cnt", C.c_void_p), ("n_cut", C.c_int32), ("cut_slot", C.c_void_p),
+                ("num_val", C.c_void_p), ("num_status", C.c_void_p), ("epoch_day", C.c_void_p),
+                ("packed_month", C.c_void_p), ("n_source", C.c_int32), ("source", C.c_void_p),
+                ("n_target", C.c_int32), ("target", C.c_void_p)]
+
+
+SIM_METHOD = {"NGRAM_COSINE": 0, "NGRAM_JACCARD": 1, "TOKEN_COSINE": 2, "TOKEN_JACCARD": 3, "NUMERIC": 4,
+              "DATE_DAYS": 5, "DATE_MONTHS": 6, "DATE_YEARS": 7}
+SIM_TIME = {"BIDIRECTIONAL": 0, "BACKWARDS": 1, "FORWARDS": 2}
+
 EPOCH_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_double, C.c_double)
 
 # name -> (restype, argtypes); every symbol include/graphemb.h declares
@@ -46,6 +62,8 @@ SIGNATURES = {
     "ge_set_graph_edges": (C.c_int, [_P, _I32, _I64, _P, _P, _P]),
     "ge_graph_sizes": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_graph_export": (C.c_int, [_P, _P, _P, _P, _P, _P, _P]),
+    "ge_similarity_pairs": (C.c_int, [_P, C.POINTER(GeSimGroup), C.POINTER(_I64), C.POINTER(_F64)]),
+    "ge_similarity_export": (C.c_int, [_P, _I64, _P, _P, _P]),
     "ge_cooc_build": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_cooc_build_rows": (C.c_int, [_P, _I32, _I32, C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_cooc_stats": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64), C.POINTER(_F64)]),

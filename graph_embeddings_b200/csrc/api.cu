@@ -159,6 +159,7 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     ge_dist_free(ctx);
+    ge_free_sim(ctx);
     ge_free_store(ctx);
     ge_free_cooc(ctx);
     ge_free_graph(ctx);

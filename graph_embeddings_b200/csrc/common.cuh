@@ -89,6 +89,7 @@ __host__ __device__ inline int32_t ge_damp_bits(int32_t cnt, int32_t hot_count) 
 }
 
 struct DistState;  // dist.cu
+struct SimState;   // sim.cu
 
 struct ge_ctx {
     ge_config cfg;
@@ -137,6 +138,7 @@ struct ge_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
     DistState* dist = nullptr;
+    SimState* sim = nullptr;  // result of the last similarity compare
 };
 
 // train.cu
@@ -151,6 +153,8 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (damped deltas)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
+// sim.cu
+void ge_free_sim(ge_ctx* ctx);
 // api.cu
 void ge_free_graph(ge_ctx* ctx);
 int ge_graph_finish(ge_ctx* ctx);

@@ -117,6 +117,73 @@ int ge_graph_sizes(ge_ctx*, int64_t* E_out, int64_t* E_in, double* flatten_secon
 int ge_graph_export(ge_ctx*, int64_t* out_off, int32_t* out_nbr, float* out_w, int64_t* in_off,
                     int32_t* in_nbr, float* in_w);
 
+/* SURVEY §8(f) row 4 — similarity edges between literals: the all-pairs compare that
+ * Rdf2GrphConverter.convert runs per predicate group just before the graph is handed over
+ * (J/convert/Rdf2GrphConverter.java:127-186, one CompareJob per source literal,
+ * J/compare/CompareJob.java:32-53: every target j >= startIndex whose vertex differs, pair kept when
+ * metric.similarity(s1, s2) >= threshold, weight (float) similarity, later added as TWO directed
+ * edges of type 0).  Strings stay on the host: the caller hands over what the metrics read —
+ * profile-based metrics (J/util/similarity/PreComputed*.java) get each literal's profile as
+ * (shingle id, count) lists sorted by id, NUMERIC / DATE_* get the parsed values.  JAROWINKLER and
+ * LEVENSHTEIN (third-party info.debatty code) are not served. */
+#define GE_SIM_NGRAM_COSINE 0  /* PreComputedNgramCosine.java:20-31,55-57  */
+#define GE_SIM_NGRAM_JACCARD 1 /* PreComputedNgramJaccard.java:28-47       */
+#define GE_SIM_TOKEN_COSINE 2  /* PreComputedTokenCosine.java:29-44        */
+#define GE_SIM_TOKEN_JACCARD 3 /* PreComputedTokenJaccard.java:32-51       */
+#define GE_SIM_NUMERIC 4       /* Numeric.java:18-44                       */
+#define GE_SIM_DATE_DAYS 5     /* Date.java:30-66, DateDays/Months/Years   */
+#define GE_SIM_DATE_MONTHS 6
+#define GE_SIM_DATE_YEARS 7
+#define GE_SIM_TIME_BIDIRECTIONAL 0 /* Configuration.SimilarityGroup.Time (Configuration.java:184-186) */
+#define GE_SIM_TIME_BACKWARDS 1
+#define GE_SIM_TIME_FORWARDS 2
+#define GE_SIM_FLAG_EMPTY 1  /* label.isEmpty()                                        */
+#define GE_SIM_FLAG_LONG 2   /* label.length() >= ngram (NGRAM_COSINE, :27)            */
+#define GE_SIM_FLAG_PARSED 4 /* DATE_*: LocalDate.parse succeeded (else similarity 0)  */
+#define GE_SIM_NUM_OK 0
+#define GE_SIM_NUM_NFE 1 /* Integer.parseInt threw NumberFormatException -> similarity 0 (Numeric.java:40-43)    */
+#define GE_SIM_NUM_OOB 2 /* substring(0, cut) past the end: uncaught, the whole CompareJob of s1 is lost (:33) */
+
+typedef struct ge_sim_group {
+    int32_t method;         /* GE_SIM_* */
+    int32_t upper_triangle; /* sourcePredicate.equals(targetPredicate) (Rdf2GrphConverter.java:50): j starts at index+1 */
+    double threshold;       /* pair kept when similarity >= threshold (CompareJob.java:46) */
+    double smooth;          /* getSmooth(): Numeric alpha / Date smooth, 0 already mapped to 1 */
+    double distance;
+    int32_t time_dir;       /* GE_SIM_TIME_* (DATE_* only) */
+    int32_t n_items;        /* distinct literal vertices of the group (source and target sets together) */
+    const int32_t* vert;      /* [n_items] graph vertex id                                      */
+    const int32_t* string_id; /* [n_items] literals with equal labels share an id (s1.equals(s2)) */
+    const uint8_t* flags;     /* [n_items] GE_SIM_FLAG_*                                        */
+    /* profile metrics: item k's profile is prof_key/prof_cnt[prof_off[k] .. prof_off[k+1]), keys ascending */
+    const int64_t* prof_off;
+    const int32_t* prof_key;
+    const int32_t* prof_cnt;
+    /* NUMERIC.  Numeric.java:29-33 cuts BOTH strings at s1's '^' position, so what s2 parses to
+     * depends on s1: the caller lists the n_cut distinct cut positions of the group (one of them may
+     * stand for "no '^': parse the whole label"), cut_slot[k] is the slot of item k's own position,
+     * and num_val / num_status[k * n_cut + c] are Integer.parseInt of item k's label cut at slot c. */
+    int32_t n_cut;
+    const int32_t* cut_slot;
+    const int32_t* num_val;
+    const uint8_t* num_status; /* GE_SIM_NUM_* */
+    /* DATE_*: LocalDate fields of the parsed labels */
+    const int64_t* epoch_day;    /* LocalDate.toEpochDay()                       */
+    const int64_t* packed_month; /* getProlepticMonth() * 32 + getDayOfMonth()   */
+    /* the two sides, as item indices in the iteration order of group.source / group.target */
+    int32_t n_source;
+    const int32_t* source;
+    int32_t n_target;
+    const int32_t* target;
+} ge_sim_group;
+
+/* runs the compare on the device and keeps the result there; count = pairs kept.  Pairs are
+ * ordered by (source index, target index) — the reference's order depends on which job finishes
+ * first. */
+int ge_similarity_pairs(ge_ctx*, const ge_sim_group* group, int64_t* count, double* seconds);
+/* copy the kept pairs out: vert[k] = source vertex, other[k] = target vertex, sim[k] = (float) similarity */
+int ge_similarity_export(ge_ctx*, int64_t cap, int32_t* vert, int32_t* other, float* sim);
+
 /* A2-A4 — new BookmarkColoring(graph, config): builds the COO on the device.
  * Outputs: nnz = coOccurrenceCount(), xmax = max().  Rows [first, first+count) only when
  * count >= 0 (multi-GPU row sharding); count < 0 = all rows. */
