@@ -42,6 +42,15 @@ public final class GraphEmb {
     /** ge_extract: (focus+context)/2 as double[V*dim], row-major (Optimizer.extractResult). */
     public static native void extract(long ctx, double[] out);
 
+    /** ge_similarity_pairs + ge_similarity_export: the CompareJob loop of one CompareGroup on the device.
+     *  Arrays are the fields of ge_sim_group (include/graphemb.h); unused ones may be null.
+     *  Returns {vert[], other[]} as int[2][count]; the similarities are written to sim[0]. */
+    public static native int[][] similarityPairs(long ctx, int method, boolean upperTriangle, double threshold,
+                                                 double smooth, double distance, int timeDir, int[] vert, int[] stringId,
+                                                 byte[] flags, long[] profOff, int[] profKey, int[] profCnt, int nCut,
+                                                 int[] cutSlot, int[] numVal, byte[] numStatus, long[] epochDay,
+                                                 long[] packedMonth, int[] source, int[] target, float[][] sim);
+
     /** ge_write_embeddings: EmbeddingTextWriter.write from the device store. */
     public static native void writeEmbeddings(long ctx, String vectorsPath, String dictPath, String header,
                                               String[] keys, byte[] types, boolean[] typeEnabled,
