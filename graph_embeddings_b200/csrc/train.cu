@@ -11,6 +11,9 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <string.h>
+
+#include <thread>
 
 namespace {
 
@@ -589,13 +592,13 @@ __global__ void store_init(float* __restrict__ W, float* __restrict__ C, int32_t
 
 // K8 — extractResult (Optimizer.java:130-140): (focus + context) / 2 in f32, widened
 template <typename T>
-__global__ void extract_avg(const float* __restrict__ W, const float* __restrict__ C, int32_t V,
+__global__ void extract_avg(const float* __restrict__ W, const float* __restrict__ C, int64_t row0, int32_t rows,
                             int32_t dim, int32_t S, T* __restrict__ out) {
-    const int64_t total = (int64_t)V * dim, stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t total = (int64_t)rows * dim, stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
         const int64_t r = k / dim;
         const int32_t d = (int32_t)(k - r * dim);
-        out[k] = (T)__fdiv_rn(__fadd_rn(W[r * S + d], C[r * S + d]), 2.0f);
+        out[k] = (T)__fdiv_rn(__fadd_rn(W[(row0 + r) * S + d], C[(row0 + r) * S + d]), 2.0f);
     }
 }
 
@@ -919,17 +922,66 @@ extern "C" int ge_cost_history(ge_ctx* ctx, double* out, int32_t cap) {
     return n;
 }
 
+// The result goes to pageable host memory (a Java double[] / numpy array), which the driver would
+// copy at 3-4 GB/s through its own staging.  Instead: row chunks through two pinned staging buffers;
+// while chunk c crosses PCIe, host threads move chunk c-1 from staging into `out` (they also take the
+// first-touch page faults of a freshly allocated destination in parallel).
 template <typename T>
 static int extract_impl(ge_ctx* ctx, T* out) {
     if (!ctx || !out) return GE_ERR_INVALID;
     if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
-    const size_t n = (size_t)ctx->V * ctx->cfg.dim;
-    T* d = nullptr;
-    GE_CUDA(cudaMalloc(&d, n * sizeof(T)));
-    extract_avg<T><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, ctx->V, ctx->cfg.dim, ctx->S, d);
-    cudaError_t e = cudaMemcpyAsync(out, d, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream);
+    const int32_t V = ctx->V, dim = ctx->cfg.dim;
+    const size_t row_bytes = (size_t)dim * sizeof(T);
+    int64_t chunk_rows = (int64_t)((size_t)(48u << 20) / row_bytes);
+    if (chunk_rows < 1) chunk_rows = 1;
+    if (chunk_rows > V) chunk_rows = V;
+    const size_t chunk_bytes = (size_t)chunk_rows * row_bytes;
+    T *d[2] = {nullptr, nullptr}, *h[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+        e = cudaMalloc(&d[k], chunk_bytes);
+        if (e == cudaSuccess) e = cudaMallocHost(&h[k], chunk_bytes);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+    }
+    unsigned nthr = std::thread::hardware_concurrency();
+    nthr = nthr < 1 ? 1 : (nthr > 8 ? 8 : nthr);
+    auto drain = [&](int64_t c) {  // chunk c: staging -> out
+        const int64_t row0 = c * chunk_rows;
+        const size_t bytes = (size_t)((V - row0) < chunk_rows ? (V - row0) : chunk_rows) * row_bytes;
+        const char* src = (const char*)h[c & 1];
+        char* dst = (char*)out + (size_t)row0 * row_bytes;
+        if (bytes < (8u << 20) || nthr == 1) { memcpy(dst, src, bytes); return; }
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nthr; t++) {
+            const size_t lo = bytes * t / nthr, hi = bytes * (t + 1) / nthr;
+            th.emplace_back([=] { memcpy(dst + lo, src + lo, hi - lo); });
+        }
+        for (auto& x : th) x.join();
+    };
+    const int64_t nchunk = (V + chunk_rows - 1) / chunk_rows;
+    for (int64_t c = 0; c < nchunk && e == cudaSuccess; c++) {
+        const int64_t row0 = c * chunk_rows;
+        const int32_t rows = (int32_t)((V - row0) < chunk_rows ? (V - row0) : chunk_rows);
+        // slot c&1 was drained two iterations ago (drain runs on this thread), so it is free
+        extract_avg<T><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, row0, rows, dim, ctx->S, d[c & 1]);
+        e = cudaMemcpyAsync(h[c & 1], d[c & 1], (size_t)rows * row_bytes, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[c & 1], ctx->stream);
+        if (c > 0 && e == cudaSuccess) {
+            e = cudaEventSynchronize(ev[(c - 1) & 1]);
+            if (e == cudaSuccess) drain(c - 1);
+        }
+    }
+    if (e == cudaSuccess && nchunk > 0) {
+        e = cudaEventSynchronize(ev[(nchunk - 1) & 1]);
+        if (e == cudaSuccess) drain(nchunk - 1);
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d);
+    for (int k = 0; k < 2; k++) {
+        cudaFree(d[k]);
+        cudaFreeHost(h[k]);
+        if (ev[k]) cudaEventDestroy(ev[k]);
+    }
     GE_CUDA(e);
     return GE_OK;
 }
