@@ -40,11 +40,12 @@ class GeSimGroup(C.Structure):
                 ("prof_cnt", C.c_void_p), ("n_cut", C.c_int32), ("cut_slot", C.c_void_p),
                 ("num_val", C.c_void_p), ("num_status", C.c_void_p), ("epoch_day", C.c_void_p),
                 ("packed_month", C.c_void_p), ("n_source", C.c_int32), ("source", C.c_void_p),
-                ("n_target", C.c_int32), ("target", C.c_void_p)]
+                ("n_target", C.c_int32), ("target", C.c_void_p), ("char_off", C.c_void_p),
+                ("chars", C.c_void_p)]
 
 
 SIM_METHOD = {"NGRAM_COSINE": 0, "NGRAM_JACCARD": 1, "TOKEN_COSINE": 2, "TOKEN_JACCARD": 3, "NUMERIC": 4,
-              "DATE_DAYS": 5, "DATE_MONTHS": 6, "DATE_YEARS": 7}
+              "DATE_DAYS": 5, "DATE_MONTHS": 6, "DATE_YEARS": 7, "JAROWINKLER": 8, "LEVENSHTEIN": 9}
 SIM_TIME = {"BIDIRECTIONAL": 0, "BACKWARDS": 1, "FORWARDS": 2}
 
 EPOCH_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_double, C.c_double)

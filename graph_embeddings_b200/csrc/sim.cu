@@ -36,6 +36,12 @@ struct SimDev {
     const int64_t *epoch_day, *packed_month;
     const int32_t *source, *target;
     int32_t n_source, n_target, nseg;
+    // JAROWINKLER / LEVENSHTEIN: labels as UTF-16 code units + per-thread scratch words, interleaved
+    // by thread (word k of thread t at scratch[k * nthreads + t]) so that lanes in step coalesce
+    const int64_t* char_off;
+    const uint16_t* chars;
+    uint32_t* scratch;
+    int64_t nthreads;
 };
 
 // Euclidean norm of a profile: Math.sqrt(sum of Math.pow(v, 2)) (TokenCosine.java:30-32,
@@ -49,10 +55,102 @@ __global__ void profile_norms(const int64_t* __restrict__ off, const int32_t* __
     norm[k] = __dsqrt_rn(s);
 }
 
+// ---- info.debatty java-string-similarity (pom.xml:50-51, version "RELEASE"; restated from the
+// published 2.0.0 source, not under /root/reference) ------------------------------------------------
+
+// NormalizedLevenshtein.similarity = 1.0 - Levenshtein.distance(s1, s2) / max(len1, len2) (double / int);
+// the distance is the textbook unit-cost one, so any exact evaluation gives the reference's value.
+// One DP row per thread in scratch (in-place update with the diagonal carried in a register).
+__device__ __forceinline__ double levenshtein_similarity(const SimDev& g, int32_t a, int32_t b, int64_t tid) {
+    const uint16_t *s1 = g.chars + g.char_off[a], *s2 = g.chars + g.char_off[b];
+    const int32_t n1 = (int32_t)(g.char_off[a + 1] - g.char_off[a]), n2 = (int32_t)(g.char_off[b + 1] - g.char_off[b]);
+    const int32_t mx = n1 > n2 ? n1 : n2, gap = n1 > n2 ? n1 - n2 : n2 - n1;
+    // distance >= |n1 - n2| and every step below is monotone under correct rounding: skip the DP
+    // when even that bound misses the threshold
+    if (!(__dsub_rn(1.0, __ddiv_rn((double)gap, (double)mx)) >= g.threshold)) return __longlong_as_double(0x7ff8000000000000LL);
+    int32_t dist;
+    if (n1 == 0) dist = n2;
+    else if (n2 == 0) dist = n1;
+    else {
+        uint32_t* row = g.scratch + tid;
+        const int64_t st = g.nthreads;
+        for (int32_t j = 0; j <= n2; j++) row[(int64_t)j * st] = (uint32_t)j;
+        for (int32_t i = 0; i < n1; i++) {
+            const uint16_t c1 = __ldg(s1 + i);
+            uint32_t diag = (uint32_t)i, left = (uint32_t)i + 1;  // v0[0], v1[0]
+            row[0] = left;
+            for (int32_t j = 0; j < n2; j++) {
+                const uint32_t up = row[(int64_t)(j + 1) * st];
+                const uint32_t sub = diag + (c1 == __ldg(s2 + j) ? 0u : 1u);
+                uint32_t v = left + 1 < up + 1 ? left + 1 : up + 1;
+                v = v < sub ? v : sub;
+                row[(int64_t)(j + 1) * st] = v;
+                diag = up;
+                left = v;
+            }
+        }
+        dist = (int32_t)row[(int64_t)n2 * st];
+    }
+    return __dsub_rn(1.0, __ddiv_rn((double)dist, (double)mx));
+}
+
+// JaroWinkler.similarity: matches() pairs every character of the shorter string with the first free
+// equal character of the longer one inside the window max(len/2 - 1, 0); transpositions = half the
+// matched characters that differ in order; prefix = common prefix (not capped).  The Jaro term is
+// evaluated in FLOAT (m is a float in the source), the Winkler boost in double.
+__device__ __forceinline__ double jaro_winkler_similarity(const SimDev& g, int32_t a, int32_t b, int64_t tid) {
+    const uint16_t *s1 = g.chars + g.char_off[a], *s2 = g.chars + g.char_off[b];
+    const int32_t n1 = (int32_t)(g.char_off[a + 1] - g.char_off[a]), n2 = (int32_t)(g.char_off[b + 1] - g.char_off[b]);
+    const uint16_t *mx = n1 > n2 ? s1 : s2, *mn = n1 > n2 ? s2 : s1;   // s1.length() > s2.length() ? s1 : s2
+    const int32_t nmx = n1 > n2 ? n1 : n2, nmn = n1 > n2 ? n2 : n1;
+    if (nmn == 0) return 0.0;  // no matches: return 0f
+    const int32_t range = nmx / 2 - 1 > 0 ? nmx / 2 - 1 : 0;
+    const int64_t st = g.nthreads;
+    uint32_t* bmax = g.scratch + tid;                                      // match_flags over max, one bit each
+    uint32_t* bmin = g.scratch + tid + (int64_t)((nmx + 31) >> 5) * st;    // match_indexes[i] != -1 over min
+    for (int32_t k = 0; k < (nmx + 31) >> 5; k++) bmax[(int64_t)k * st] = 0u;
+    for (int32_t k = 0; k < (nmn + 31) >> 5; k++) bmin[(int64_t)k * st] = 0u;
+    int32_t matches = 0;
+    for (int32_t mi = 0; mi < nmn; mi++) {
+        const uint16_t c1 = __ldg(mn + mi);
+        const int32_t lo = mi - range > 0 ? mi - range : 0, hi = mi + range + 1 < nmx ? mi + range + 1 : nmx;
+        for (int32_t xi = lo; xi < hi; xi++) {
+            const uint32_t w = bmax[(int64_t)(xi >> 5) * st];
+            if (!((w >> (xi & 31)) & 1u) && c1 == __ldg(mx + xi)) {
+                bmax[(int64_t)(xi >> 5) * st] = w | (1u << (xi & 31));
+                bmin[(int64_t)(mi >> 5) * st] |= 1u << (mi & 31);
+                matches++;
+                break;
+            }
+        }
+    }
+    if (matches == 0) return 0.0;
+    int32_t differ = 0, xi = 0;  // walk the matched characters of both strings in order
+    for (int32_t mi = 0; mi < nmn; mi++) {
+        if (!((bmin[(int64_t)(mi >> 5) * st] >> (mi & 31)) & 1u)) continue;
+        while (!((bmax[(int64_t)(xi >> 5) * st] >> (xi & 31)) & 1u)) xi++;
+        if (__ldg(mn + mi) != __ldg(mx + xi)) differ++;
+        xi++;
+    }
+    int32_t prefix = 0;
+    for (int32_t k = 0; k < nmn; k++) { if (__ldg(s1 + k) == __ldg(s2 + k)) prefix++; else break; }
+    const float m = (float)matches;
+    const float jf = __fdiv_rn(__fadd_rn(__fadd_rn(__fdiv_rn(m, (float)n1), __fdiv_rn(m, (float)n2)),
+                                         __fdiv_rn(__fsub_rn(m, (float)(differ / 2)), m)), 3.0f);
+    const double j = (double)jf;
+    if (!(j > 0.7)) return j;
+    const double coef = fmin(0.1, __ddiv_rn(1.0, (double)nmx));
+    return __dadd_rn(j, __dmul_rn(__dmul_rn(coef, (double)prefix), __dsub_rn(1.0, j)));
+}
+
 // metric.similarity(label[a], label[b]); oob = the reference would have thrown out of the job
-__device__ __forceinline__ double pair_similarity(const SimDev& g, int32_t a, int32_t b, bool& oob) {
+__device__ __forceinline__ double pair_similarity(const SimDev& g, int32_t a, int32_t b, bool& oob, int64_t tid) {
     const uint8_t fa = g.flags[a], fb = g.flags[b];
     const bool same = g.sid[a] == g.sid[b];
+    if (g.method >= GE_SIM_JAROWINKLER) {
+        if (same) return 1.0;  // s1.equals(s2)
+        return g.method == GE_SIM_LEVENSHTEIN ? levenshtein_similarity(g, a, b, tid) : jaro_winkler_similarity(g, a, b, tid);
+    }
     if (g.method <= GE_SIM_TOKEN_JACCARD) {
         if (same) return 1.0;  // s1.equals(s2)
         const bool jaccard = g.method == GE_SIM_NGRAM_JACCARD || g.method == GE_SIM_TOKEN_JACCARD;
@@ -138,7 +236,7 @@ __global__ void __launch_bounds__(256) sim_pass(SimDev g, uint32_t* __restrict__
                 vb = g.vert[b];
                 if (vb != va) {  // CompareJob.java:40
                     bool oob = false;
-                    sim = pair_similarity(g, a, b, oob);
+                    sim = pair_similarity(g, a, b, oob, (int64_t)blockIdx.x * blockDim.x + threadIdx.x);
                     dead |= oob;
                     hit = !oob && sim >= g.threshold;  // NaN fails, as in Java
                 }
@@ -260,10 +358,12 @@ struct Scratch {  // device buffers of one call, released on every exit path
 extern "C" int ge_similarity_pairs(ge_ctx* ctx, const ge_sim_group* grp, int64_t* count, double* seconds) {
     if (!ctx || !grp) return GE_ERR_INVALID;
     const int32_t n = grp->n_items, method = grp->method;
-    if (method < GE_SIM_NGRAM_COSINE || method > GE_SIM_DATE_YEARS) { ctx->err = "unsupported similarity method (JAROWINKLER / LEVENSHTEIN stay on the host)"; return GE_ERR_INVALID; }
+    if (method < GE_SIM_NGRAM_COSINE || method > GE_SIM_LEVENSHTEIN) { ctx->err = "unsupported similarity method"; return GE_ERR_INVALID; }
     if (n < 0 || grp->n_source < 0 || grp->n_target < 0 || (n > 0 && (!grp->vert || !grp->string_id || !grp->flags)) ||
         (grp->n_source > 0 && !grp->source) || (grp->n_target > 0 && !grp->target)) { ctx->err = "bad similarity group arguments"; return GE_ERR_INVALID; }
-    const bool profile = method <= GE_SIM_TOKEN_JACCARD, numeric = method == GE_SIM_NUMERIC, date = method >= GE_SIM_DATE_DAYS;
+    const bool profile = method <= GE_SIM_TOKEN_JACCARD, numeric = method == GE_SIM_NUMERIC;
+    const bool date = method >= GE_SIM_DATE_DAYS && method <= GE_SIM_DATE_YEARS, text = method >= GE_SIM_JAROWINKLER;
+    if (n > 0 && text && (!grp->char_off || (grp->char_off[n] > 0 && !grp->chars))) { ctx->err = "JAROWINKLER / LEVENSHTEIN without labels"; return GE_ERR_INVALID; }
     if (n > 0 && profile && (!grp->prof_off || (grp->prof_off[n] > 0 && (!grp->prof_key || !grp->prof_cnt)))) { ctx->err = "profile metric without profiles"; return GE_ERR_INVALID; }
     if (n > 0 && numeric && (grp->n_cut <= 0 || !grp->cut_slot || !grp->num_val || !grp->num_status)) { ctx->err = "NUMERIC without parsed values"; return GE_ERR_INVALID; }
     if (n > 0 && date && (!grp->epoch_day || !grp->packed_month)) { ctx->err = "DATE_* without parsed dates"; return GE_ERR_INVALID; }
@@ -303,9 +403,22 @@ extern "C" int ge_similarity_pairs(ge_ctx* ctx, const ge_sim_group* grp, int64_t
         GE_CUDA(sc.up(grp->cut_slot, (size_t)n, &g.cut_slot, st));
         GE_CUDA(sc.up(grp->num_val, (size_t)n * grp->n_cut, &g.num_val, st));
         GE_CUDA(sc.up(grp->num_status, (size_t)n * grp->n_cut, &g.num_status, st));
-    } else {
+    } else if (date) {
         GE_CUDA(sc.up(grp->epoch_day, (size_t)n, &g.epoch_day, st));
         GE_CUDA(sc.up(grp->packed_month, (size_t)n, &g.packed_month, st));
+    }
+    int64_t scratch_words = 0;  // per thread
+    if (text) {
+        GE_CUDA(sc.up(grp->char_off, (size_t)n + 1, &g.char_off, st));
+        GE_CUDA(sc.up(grp->chars, (size_t)grp->char_off[n], &g.chars, st));
+        int64_t longest = 0;
+        for (int32_t k = 0; k < n; k++) {
+            const int64_t len = grp->char_off[k + 1] - grp->char_off[k];
+            if (len < 0) { ctx->err = "label offsets must not decrease"; return GE_ERR_INVALID; }
+            longest = len > longest ? len : longest;
+        }
+        // LEVENSHTEIN: one DP row; JAROWINKLER: two bit sets
+        scratch_words = method == GE_SIM_LEVENSHTEIN ? longest + 1 : 2 * ((longest + 31) / 32);
     }
     const int64_t nwork = (int64_t)g.n_source * g.nseg;
     const int64_t ntile = (nwork + SCAN_TILE - 1) / SCAN_TILE;
@@ -322,7 +435,13 @@ extern "C" int ge_similarity_pairs(ge_ctx* ctx, const ge_sim_group* grp, int64_t
     if (!ctx->ev0) { GE_CUDA(cudaEventCreate(&ctx->ev0)); GE_CUDA(cudaEventCreate(&ctx->ev1)); }
     GE_CUDA(cudaEventRecord(ctx->ev0, st));
     const int64_t want = (nwork * 32 + 255) / 256;
-    const int grid = (int)(want < (int64_t)ctx->sm_count * 8 ? (want < 1 ? 1 : want) : (int64_t)ctx->sm_count * 8);
+    int grid = (int)(want < (int64_t)ctx->sm_count * 8 ? (want < 1 ? 1 : want) : (int64_t)ctx->sm_count * 8);
+    if (scratch_words > 0) {  // bound the scratch to 2 GB by running fewer blocks when labels are very long
+        const int64_t fit = ((int64_t)2 << 30) / (256 * 4 * scratch_words);
+        if (grid > fit) grid = fit < 1 ? 1 : (int)fit;
+        g.nthreads = (int64_t)grid * 256;
+        GE_CUDA(sc.make((size_t)(g.nthreads * scratch_words), &g.scratch));
+    }
     sim_pass<false><<<grid, 256, 0, st>>>(g, d_cnt, nullptr, d_dead, nullptr, nullptr, nullptr);
     drop_dead_rows<<<(unsigned)((nwork + 255) / 256), 256, 0, st>>>(d_cnt, d_dead, g.nseg, nwork);
     scan_tile_totals<<<(unsigned)ntile, 256, 0, st>>>(d_cnt, nwork, d_tile);

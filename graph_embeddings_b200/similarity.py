@@ -8,7 +8,7 @@
 What stays on the host is what the Java host would do in the shim: turning each literal's label into
 the numbers the metric reads (shingle / token profiles as id lists, Integer.parseInt, LocalDate
 fields).  The O(|source| x |target|) compare itself is ge_similarity_pairs in libgraphemb.so; there
-is no CPU fallback.  JAROWINKLER and LEVENSHTEIN (third-party info.debatty code) are not served.
+is no CPU fallback.  JAROWINKLER and LEVENSHTEIN get the labels themselves (UTF-16 code units).
 """
 from __future__ import annotations
 
@@ -259,6 +259,11 @@ class CompareGroup:
                     else:
                         val[k, c] = v
             keep.update(n_cut=len(cuts), cut_slot=np.array([slot[h] for h in hats], np.int32), num_val=val, num_status=st)
+        elif m in ("JAROWINKLER", "LEVENSHTEIN"):
+            codes = [np.frombuffer(u.encode("utf-16-le", "surrogatepass"), np.uint16) for u in units]
+            off = np.zeros(n + 1, np.int64)
+            np.cumsum([len(c) for c in codes], out=off[1:])
+            keep.update(char_off=off, chars=np.concatenate(codes + [np.zeros(1, np.uint16)]))
         else:
             ep, pk = np.zeros(n, np.int64), np.zeros(n, np.int64)
             for k, u in enumerate(units):
@@ -287,7 +292,8 @@ class CompareGroup:
         g.time_dir, g.n_items = _lib.SIM_TIME[self.time], len(verts)
         g.n_source, g.n_target, g.n_cut = len(src), len(dst), int(d.get("n_cut", 0))
         arrays = {"vert": vert, "string_id": d["sid"], "flags": d["flags"], "source": s_idx, "target": t_idx}
-        for name in ("prof_off", "prof_key", "prof_cnt", "cut_slot", "num_val", "num_status", "epoch_day", "packed_month"):
+        for name in ("prof_off", "prof_key", "prof_cnt", "cut_slot", "num_val", "num_status", "epoch_day", "packed_month",
+                     "char_off", "chars"):
             if name in d:
                 arrays[name] = d[name]
         arrays = {k: np.ascontiguousarray(a) for k, a in arrays.items()}

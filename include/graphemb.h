@@ -124,8 +124,9 @@ int ge_graph_export(ge_ctx*, int64_t* out_off, int32_t* out_nbr, float* out_w, i
  * metric.similarity(s1, s2) >= threshold, weight (float) similarity, later added as TWO directed
  * edges of type 0).  Strings stay on the host: the caller hands over what the metrics read —
  * profile-based metrics (J/util/similarity/PreComputed*.java) get each literal's profile as
- * (shingle id, count) lists sorted by id, NUMERIC / DATE_* get the parsed values.  JAROWINKLER and
- * LEVENSHTEIN (third-party info.debatty code) are not served. */
+ * (shingle id, count) lists sorted by id, NUMERIC / DATE_* get the parsed values,
+ * JAROWINKLER / LEVENSHTEIN (info.debatty java-string-similarity, Configuration.java:212-215) get the
+ * labels themselves as UTF-16 code units. */
 #define GE_SIM_NGRAM_COSINE 0  /* PreComputedNgramCosine.java:20-31,55-57  */
 #define GE_SIM_NGRAM_JACCARD 1 /* PreComputedNgramJaccard.java:28-47       */
 #define GE_SIM_TOKEN_COSINE 2  /* PreComputedTokenCosine.java:29-44        */
@@ -134,6 +135,8 @@ int ge_graph_export(ge_ctx*, int64_t* out_off, int32_t* out_nbr, float* out_w, i
 #define GE_SIM_DATE_DAYS 5     /* Date.java:30-66, DateDays/Months/Years   */
 #define GE_SIM_DATE_MONTHS 6
 #define GE_SIM_DATE_YEARS 7
+#define GE_SIM_JAROWINKLER 8   /* info.debatty JaroWinkler.similarity (threshold 0.7, float Jaro term) */
+#define GE_SIM_LEVENSHTEIN 9   /* info.debatty NormalizedLevenshtein.similarity = 1 - distance / max length */
 #define GE_SIM_TIME_BIDIRECTIONAL 0 /* Configuration.SimilarityGroup.Time (Configuration.java:184-186) */
 #define GE_SIM_TIME_BACKWARDS 1
 #define GE_SIM_TIME_FORWARDS 2
@@ -175,6 +178,9 @@ typedef struct ge_sim_group {
     const int32_t* source;
     int32_t n_target;
     const int32_t* target;
+    /* JAROWINKLER / LEVENSHTEIN: item k's label is chars[char_off[k] .. char_off[k+1]) (UTF-16 code units) */
+    const int64_t* char_off;
+    const uint16_t* chars;
 } ge_sim_group;
 
 /* runs the compare on the device and keeps the result there; count = pairs kept.  Pairs are

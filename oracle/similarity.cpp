@@ -8,13 +8,15 @@
 //   J/util/similarity/*.java                  (the metrics; cited at each function)
 // Third-party code on this path that is NOT under /root/reference: info.debatty
 // java-string-similarity (pom.xml:50-51, version "RELEASE" = unpinned; 2.0.0 is the last release).
-// Only its ShingleBased.getProfile is needed (k-shingles of the string after collapsing every
-// whitespace run to one blank, with occurrence counts); restated from its published source.
+// Its ShingleBased.getProfile (k-shingles of the string after collapsing every whitespace run to one
+// blank, with occurrence counts), JaroWinkler and NormalizedLevenshtein are restated from the
+// published 2.0.0 source.
 // JDK pieces restated from their Javadoc: String.trim, Integer.parseInt (ASCII digits only here),
 // DateTimeFormatter.BASIC_ISO_DATE (strict; optional offset Z / +HH / +HHMM / +HHMMss),
 // LocalDate.toEpochDay / monthsUntil.  Strings are UTF-16 code units, as in Java.
 //
 // Build: -O2 -ffp-contract=off -fno-fast-math.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <map>
@@ -27,7 +29,7 @@ namespace {
 using ustr = std::u16string;
 using Profile = std::map<ustr, int32_t>;  // HashMap<String,Integer>: only order-independent uses below
 
-enum Method { NGRAM_COSINE = 0, NGRAM_JACCARD, TOKEN_COSINE, TOKEN_JACCARD, NUMERIC, DATE_DAYS, DATE_MONTHS, DATE_YEARS };
+enum Method { NGRAM_COSINE = 0, NGRAM_JACCARD, TOKEN_COSINE, TOKEN_JACCARD, NUMERIC, DATE_DAYS, DATE_MONTHS, DATE_YEARS, JAROWINKLER, LEVENSHTEIN };
 enum TimeDir { BIDIRECTIONAL = 0, BACKWARDS = 1, FORWARDS = 2 };
 
 struct JobDied {};  // an exception that CompareJob.call does not catch
@@ -101,6 +103,65 @@ int32_t dot_product(const Profile& a, const Profile& b) {  // TokenCosine.java:3
 }
 
 double cosine(const Profile& a, const Profile& b) { return dot_product(a, b) / (norm(a) * norm(b)); }
+
+// ---- info.debatty NormalizedLevenshtein / Levenshtein (published 2.0.0 source) ---------------
+// Levenshtein.distance: two-row DP, unit costs, returned as double; NormalizedLevenshtein.distance =
+// that / max(len1, len2) (0 for equal strings or two empty ones); similarity = 1.0 - distance.
+double levenshtein_distance(const ustr& s1, const ustr& s2) {
+    if (s1 == s2) return 0;
+    if (s1.empty()) return (double)s2.size();
+    if (s2.empty()) return (double)s1.size();
+    std::vector<int32_t> v0(s2.size() + 1), v1(s2.size() + 1);
+    for (size_t i = 0; i < v0.size(); i++) v0[i] = (int32_t)i;
+    for (size_t i = 0; i < s1.size(); i++) {
+        v1[0] = (int32_t)i + 1;
+        for (size_t j = 0; j < s2.size(); j++) {
+            const int32_t cost = s1[i] == s2[j] ? 0 : 1;
+            v1[j + 1] = std::min(v1[j] + 1, std::min(v0[j + 1] + 1, v0[j] + cost));
+        }
+        std::swap(v0, v1);
+    }
+    return (double)v0[s2.size()];
+}
+
+double normalized_levenshtein(const ustr& s1, const ustr& s2) {
+    if (s1 == s2) return 1.0 - 0;
+    const int32_t m_len = (int32_t)std::max(s1.size(), s2.size());
+    if (m_len == 0) return 1.0 - 0;
+    return 1.0 - levenshtein_distance(s1, s2) / m_len;
+}
+
+// ---- info.debatty JaroWinkler (published 2.0.0 source; threshold 0.7, JW_COEF 0.1) -----------
+double jaro_winkler(const ustr& s1, const ustr& s2) {
+    if (s1 == s2) return 1;
+    // matches(): {matches, transpositions / 2, prefix, max.length()}
+    const ustr &mx = s1.size() > s2.size() ? s1 : s2, &mn = s1.size() > s2.size() ? s2 : s1;
+    const int32_t range = std::max((int32_t)mx.size() / 2 - 1, 0);
+    std::vector<int32_t> match_indexes(mn.size(), -1);
+    std::vector<char> match_flags(mx.size(), 0);
+    int32_t matches = 0;
+    for (int32_t mi = 0; mi < (int32_t)mn.size(); mi++) {
+        const char16_t c1 = mn[mi];
+        for (int32_t xi = std::max(mi - range, 0), xn = std::min(mi + range + 1, (int32_t)mx.size()); xi < xn; xi++) {
+            if (!match_flags[xi] && c1 == mx[xi]) { match_indexes[mi] = xi; match_flags[xi] = 1; matches++; break; }
+        }
+    }
+    ustr ms1, ms2;
+    for (size_t i = 0; i < mn.size(); i++) if (match_indexes[i] != -1) ms1.push_back(mn[i]);
+    for (size_t i = 0; i < mx.size(); i++) if (match_flags[i]) ms2.push_back(mx[i]);
+    int32_t transpositions = 0;
+    for (size_t k = 0; k < ms1.size(); k++) if (ms1[k] != ms2[k]) transpositions++;
+    int32_t prefix = 0;
+    for (size_t k = 0; k < mn.size(); k++) { if (s1[k] == s2[k]) prefix++; else break; }
+    const int32_t mtp[4] = {matches, transpositions / 2, prefix, (int32_t)mx.size()};
+    // similarity(): the Jaro term is float arithmetic (m is a float), widened afterwards
+    const float m = (float)mtp[0];
+    if (m == 0) return 0.0f;
+    const double j = ((m / (float)s1.size() + m / (float)s2.size() + (m - (float)mtp[1]) / m)) / (float)3;
+    double jw = j;
+    if (j > 0.7) jw = j + std::min(0.1, 1.0 / mtp[3]) * mtp[2] * (1 - j);
+    return jw;
+}
 
 // ---- Integer.parseInt ------------------------------------------------------------------------
 bool parse_int(const ustr& s, int32_t* out) {
@@ -243,6 +304,8 @@ int64_t orc_sim_pairs(int32_t method, int32_t ngram, double threshold, double sm
                         break;
                     case TOKEN_COSINE: sim = s1 == s2 ? 1 : cosine(prof[a], prof[b]); break;
                     case NUMERIC: sim = numeric(s1, s2, smooth, distance); break;
+                    case JAROWINKLER: sim = jaro_winkler(s1, s2); break;
+                    case LEVENSHTEIN: sim = normalized_levenshtein(s1, s2); break;
                     default: sim = date(s1, s2, method, smooth, distance, time_dir); break;
                 }
             } catch (const JobDied&) { died = true; break; }

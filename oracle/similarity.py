@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle_sim.so")
 
 METHOD = {"NGRAM_COSINE": 0, "NGRAM_JACCARD": 1, "TOKEN_COSINE": 2, "TOKEN_JACCARD": 3, "NUMERIC": 4,
-          "DATE_DAYS": 5, "DATE_MONTHS": 6, "DATE_YEARS": 7}
+          "DATE_DAYS": 5, "DATE_MONTHS": 6, "DATE_YEARS": 7, "JAROWINKLER": 8, "LEVENSHTEIN": 9}
 TIME = {"bidirectional": 0, "backwards": 1, "forwards": 2}
 
 _lib = None

@@ -31,6 +31,64 @@ def pair(g, d, a, b):
         na, nb = math.sqrt(sum(v * v for v in ka.values())), math.sqrt(sum(v * v for v in kb.values()))
         den = na * nb
         return (dot / den if den else float("nan")), False
+    if m in ("JAROWINKLER", "LEVENSHTEIN"):
+        if same:
+            return 1.0, False
+        off, ch = d["char_off"], d["chars"]
+        s1, s2 = list(ch[off[a]:off[a + 1]]), list(ch[off[b]:off[b + 1]])
+        n1, n2 = len(s1), len(s2)
+        if m == "LEVENSHTEIN":
+            mx = max(n1, n2)
+            if not (1.0 - abs(n1 - n2) / mx >= g.threshold):
+                return float("nan"), False
+            if n1 == 0 or n2 == 0:
+                dist = n1 + n2
+            else:
+                row = list(range(n2 + 1))
+                for i in range(n1):
+                    diag, left = i, i + 1
+                    row[0] = left
+                    for j in range(n2):
+                        up = row[j + 1]
+                        v = min(left + 1, up + 1, diag + (0 if s1[i] == s2[j] else 1))
+                        row[j + 1] = v
+                        diag, left = up, v
+                dist = row[n2]
+            return 1.0 - dist / mx, False
+        big, small = (s1, s2) if n1 > n2 else (s2, s1)
+        if not small:
+            return 0.0, False
+        rng_ = max(len(big) // 2 - 1, 0)
+        fb_, fs_ = [False] * len(big), [False] * len(small)
+        matches = 0
+        for mi, c1 in enumerate(small):
+            for xi in range(max(mi - rng_, 0), min(mi + rng_ + 1, len(big))):
+                if not fb_[xi] and c1 == big[xi]:
+                    fb_[xi] = fs_[mi] = True
+                    matches += 1
+                    break
+        if matches == 0:
+            return 0.0, False
+        differ, xi = 0, 0
+        for mi in range(len(small)):
+            if not fs_[mi]:
+                continue
+            while not fb_[xi]:
+                xi += 1
+            differ += small[mi] != big[xi]
+            xi += 1
+        prefix = 0
+        for k in range(len(small)):
+            if s1[k] == s2[k]:
+                prefix += 1
+            else:
+                break
+        f = np.float32
+        mm = f(matches)
+        j = float((mm / f(n1) + mm / f(n2) + (mm - f(differ // 2)) / mm) / f(3))
+        if not j > 0.7:
+            return j, False
+        return j + min(0.1, 1.0 / len(big)) * prefix * (1 - j), False
     if (fa | fb) & 1:
         return 0.0, False
     if same:
@@ -103,5 +161,8 @@ if __name__ == "__main__":
     for m in ("DATE_DAYS", "DATE_MONTHS", "DATE_YEARS"):
         for t in ("bidirectional", "backwards", "forwards"):
             T.test_dates_match_oracle(None, m, t); print("ok", m, t, flush=True)
+    for m, thr in (("JAROWINKLER", 0.9), ("LEVENSHTEIN", 0.75)):
+        for upper in (True, False):
+            T.test_string_metrics_match_oracle(None, m, thr, upper); print("ok", m, upper, flush=True)
     if len(sys.argv) > 1:
         T.test_many_segments_and_scan_tiles(None); print("ok big")

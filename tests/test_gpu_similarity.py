@@ -1,6 +1,6 @@
 """Similarity edges on the device against the CPU oracle, through the C ABI:
-same pairs in the same order; similarities bit-equal for the profile metrics (integer work plus one
-correctly rounded division / sqrt), within one f32 ulp for NUMERIC / DATE_* (Math.pow vs CUDA pow)."""
+same pairs in the same order; similarities bit-equal for the profile and string metrics (integer work
+plus a few correctly rounded IEEE operations), within one f32 ulp for NUMERIC / DATE_* (Math.pow vs CUDA pow)."""
 import numpy as np
 import pytest
 
@@ -149,6 +149,23 @@ def test_dates_match_oracle(native, method, time):
     check(got, exp, exact=False)
 
 
+@pytest.mark.parametrize("method,thr", [("JAROWINKLER", 0.9), ("LEVENSHTEIN", 0.75)])
+@pytest.mark.parametrize("upper", [True, False])
+def test_string_metrics_match_oracle(native, method, thr, upper):
+    """character-level metrics: labels go to the device as UTF-16; long labels exercise the scratch rows"""
+    rng = np.random.default_rng(17)
+    n = 600
+    labels = name_labels(rng, n)
+    for k in range(0, n, 97):
+        labels[k] = labels[k] * 9 + "x" * int(rng.integers(0, 40))          # up to ~200 code units
+    vert = rng.permutation(3000)[:n]
+    cfg = {"sourcePredicate": "p", "targetPredicate": "p" if upper else "q", "method": method, "threshold": thr}
+    src, dst = (range(n), range(n)) if upper else (range(0, 350), range(250, n))
+    got, exp, _ = run_group(native, cfg, labels, vert, src, dst)
+    assert len(exp[0]) > 100
+    check(got, exp, exact=True)
+
+
 def test_empty_sides_and_errors(native):
     g = S.CompareGroup({"predicate": "p", "method": "token_cosine", "threshold": 0.5})
     v, o, s = g.compare(native, {})
@@ -159,7 +176,7 @@ def test_empty_sides_and_errors(native):
     import ctypes as C
     from graph_embeddings_b200 import GraphEmbError, _lib
     bad = _lib.GeSimGroup()
-    bad.method = 9                                           # LEVENSHTEIN: not served
+    bad.method = 10                                          # past LEVENSHTEIN
     with pytest.raises(GraphEmbError):
         native.ck(native.L.ge_similarity_pairs(native.h, C.byref(bad), None, None))
 

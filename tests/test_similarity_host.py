@@ -140,5 +140,22 @@ def test_compare_group_config_defaults():
     assert g.upperTriangle and g.ngram == 3 and g.smooth == 1.0 and g.pattern == "iso" and g.time == "BIDIRECTIONAL"
     g = S.CompareGroup({"sourcePredicate": "p", "targetPredicate": "q", "method": "DATE_DAYS", "smooth": 0, "time": "forwards"})
     assert not g.upperTriangle and g.smooth == 1.0 and g.time == "FORWARDS"
+    assert S.CompareGroup({"predicate": "p", "method": "jarowinkler"}).method == "JAROWINKLER"
     with pytest.raises(ValueError):
-        S.CompareGroup({"predicate": "p", "method": "jarowinkler"})
+        S.CompareGroup({"predicate": "p", "method": "soundex"})
+
+
+def test_string_metrics_known_answers():
+    """Jaro-Winkler / normalized Levenshtein of info.debatty java-string-similarity (not under
+    /root/reference): the classic published values, in the library's float-then-double arithmetic."""
+    f = np.float32
+    m, t = f(6), 1                                           # MARTHA / MARHTA: 6 matches, 1 transposition, prefix 3
+    j = float((m / f(6) + m / f(6) + (m - f(t)) / m) / f(3))
+    assert one("JAROWINKLER", "MARTHA", "MARHTA") == f(j + min(0.1, 1 / 6) * 3 * (1 - j))
+    assert abs(one("JAROWINKLER", "DWAYNE", "DUANE") - 0.84) < 1e-6
+    assert abs(one("JAROWINKLER", "DIXON", "DICKSONX") - 0.813333) < 1e-6
+    assert one("JAROWINKLER", "abc", "xyz") == 0.0 and one("JAROWINKLER", "", "xyz") == 0.0
+    assert one("JAROWINKLER", "same", "same") == 1.0
+    assert one("LEVENSHTEIN", "kitten", "sitting") == f(1 - 3 / 7)
+    assert one("LEVENSHTEIN", "", "abc") == 0.0 and one("LEVENSHTEIN", "abc", "abc") == 1.0 and one("LEVENSHTEIN", "", "") is not None
+    assert one("LEVENSHTEIN", "flaw", "lawn") == f(0.5)
