@@ -49,7 +49,8 @@ public final class GraphEmb {
                                                  double smooth, double distance, int timeDir, int[] vert, int[] stringId,
                                                  byte[] flags, long[] profOff, int[] profKey, int[] profCnt, int nCut,
                                                  int[] cutSlot, int[] numVal, byte[] numStatus, long[] epochDay,
-                                                 long[] packedMonth, int[] source, int[] target, float[][] sim);
+                                                 long[] packedMonth, int[] source, int[] target, long[] charOff, char[] chars,
+                                                 float[][] sim);
 
     /** ge_write_embeddings: EmbeddingTextWriter.write from the device store. */
     public static native void writeEmbeddings(long ctx, String vectorsPath, String dictPath, String header,

@@ -38,17 +38,20 @@ public final class NativeSimilarity {
         final int[] stringId = new int[n]; final byte[] flags = new byte[n];
         final Map<String, Integer> ids = new HashMap<>();
         final int method = cfg.getMethodEnum().ordinal();           // NGRAM_COSINE .. TOKEN_JACCARD = 0..3
-        final int geMethod = method <= 3 ? method : method - 2;     // JAROWINKLER, LEVENSHTEIN (4, 5) are not served
-        if (method == 4 || method == 5) throw new IllegalArgumentException("not served on the device: " + cfg.getMethod());
+        final int geMethod = method <= 3 ? method : method <= 5 ? method + 4 : method - 2;   // JAROWINKLER, LEVENSHTEIN -> 8, 9
         for (int k = 0; k < n; k++) {
             label[k] = labels.getValueAsString(vert[k]);
             stringId[k] = ids.computeIfAbsent(label[k], s -> ids.size());
             if (label[k].isEmpty()) flags[k] |= 1;
             if (label[k].length() >= cfg.getNgram()) flags[k] |= 2;
         }
-        long[] profOff = null, epochDay = null, packed = null; int[] profKey = null, profCnt = null, cutSlot = null, numVal = null;
-        byte[] numStatus = null; int nCut = 0;
-        if (geMethod <= 3) {                                        // shingle / token ids, sorted per literal
+        long[] profOff = null, epochDay = null, packed = null, charOff = null; int[] profKey = null, profCnt = null, cutSlot = null, numVal = null;
+        byte[] numStatus = null; int nCut = 0; char[] chars = null;
+        if (geMethod >= 8) {                                        // character metrics: the labels themselves
+            final StringBuilder sb = new StringBuilder(); charOff = new long[n + 1];
+            for (int k = 0; k < n; k++) { sb.append(label[k]); charOff[k + 1] = sb.length(); }
+            chars = sb.toString().toCharArray();
+        } else if (geMethod <= 3) {                                        // shingle / token ids, sorted per literal
             final Map<String, Integer> vocab = new HashMap<>();
             final List<int[]> rows = new ArrayList<>(); profOff = new long[n + 1];
             for (int k = 0; k < n; k++) {
@@ -90,7 +93,7 @@ public final class NativeSimilarity {
         final float[][] sim = new float[1][];
         final int[][] vo = GraphEmb.similarityPairs(ctx, geMethod, group.upperTriangle, group.threshold, cfg.getSmooth(),
                 cfg.getDistance(), (cfg.getTimeEnum().ordinal() + 1) % 3 /* BACKWARDS, FORWARDS, BIDIRECTIONAL -> 1, 2, 0 */,
-                vert, stringId, flags, profOff, profKey, profCnt, nCut, cutSlot, numVal, numStatus, epochDay, packed, s, t, sim);
+                vert, stringId, flags, profOff, profKey, profCnt, nCut, cutSlot, numVal, numStatus, epochDay, packed, s, t, charOff, chars, sim);
         final Result r = new Result(); r.vert = vo[0]; r.other = vo[1]; r.similarity = sim[0];
         return r;
     }
