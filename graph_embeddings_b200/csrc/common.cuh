@@ -130,7 +130,7 @@ struct ge_ctx {
     std::vector<int32_t> h_perm;  // GE_ORDER_JAVA host replay
     JavaLcg rng{0};               // stream position after init (GE_ORDER_JAVA)
     double* d_cost = nullptr;     // epoch cost accumulator
-    bool any_hot = false;         // packed nonzeros carry hub flags
+    bool any_hot = false;         // packed nonzeros carry hub damping exponents
     int32_t epoch = 0;
     std::vector<double> history;
     double update_seconds = 0;
@@ -146,7 +146,7 @@ int ge_train_prepare(ge_ctx* ctx);  // pack nonzeros, allocate cost/perm
 int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, float* C,
                      const int32_t* perm, uint64_t order_key, double* d_cost, cudaStream_t st,
                      int64_t span /* ids addressable on the smaller side: bounds concurrency */,
-                     bool any_hot /* some entries carry hub flags: use the HOT kernel */,
+                     bool any_hot /* some entries carry hub damping exponents: use the HOT kernel variant */,
                      unsigned long long* queue /* zeroed device counter: dynamic batch claiming; nullptr = static */);
 void ge_free_store(ge_ctx* ctx);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);

@@ -73,7 +73,7 @@ struct DistState {
     int head = 0;                     // slot of the window's first block
     int sub = 0;                      // sub-epochs done in the current rotation (block ids derive from it)
     double comm_seconds = 0;
-    std::vector<int32_t> bucket_hot;  // bucket has entries with hub flags -> HOT kernel
+    std::vector<int32_t> bucket_hot;  // bucket has entries with damping exponents -> HOT kernel variant
     cudaEvent_t c0 = nullptr, c1 = nullptr;
 };
 
@@ -138,7 +138,7 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
         NzEntry e;
         e.i = i;             // W index: local to the rank's row range
         e.j = j - cb * Bs;   // C index: local to the column block
-        // hub flags (train.cu ge_hot_count): expected occurrences inside THIS bucket — a row's
+        // damping exponents of hubs (train.cu ge_hot_count, common.cuh ge_damp_bits): expected occurrences inside THIS bucket — a row's
         // nonzeros spread over nb column blocks, a column's over the rank's m row blocks
         const int32_t ki = ge_damp_bits(cnt_i[i] / (nb * P), hot_cnt[b]), kj = ge_damp_bits(cnt_j[j] / m, hot_cnt[b]);
         if (ki) { e.i |= ki << GE_ID_BITS; any_hot[b] = 1; }

@@ -809,8 +809,10 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 // `launch_nnz` nonzeros, more than GE_HOT_WRITERS (default 16) warps are expected to sit on it at
 // once: red.add would then ADD that many stale-gradient steps (measured on Zipf(1) columns: clean at 16,
 // first-epoch loss 3x too high at 24 inside column blocks, NaN from 32; R-MAT matrices tolerate ~40-70; NaN at
-// ~100-250 on Zipf columns), whereas a plain store keeps one of them (the reference's own racy
-// semantics, Adagrad.java:76-80).  Returns the occurrence count from which an id is hot.
+// ~100-250 on Zipf columns), whereas the reference's racy plain stores keep about one of them
+// (Adagrad.java:76-80).  Hot ids get a damping exponent (common.cuh ge_damp_bits) that scales their
+// deltas so the sum stays below GE_HOT_WRITERS full steps.  Returns the occurrence count from which
+// an id is hot.
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
     static const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
