@@ -72,3 +72,19 @@ def test_configuration_check_mirrors_reference_messages():
         bad = Configuration(**{**ok.__dict__, **mut})
         with pytest.raises(InvalidConfigurationException, match=msg):
             Configuration.check(bad)
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under the package may import, load or link it, and
+    the shared library must not depend on it either."""
+    import subprocess
+    pkg = os.path.join(ROOT, "graph_embeddings_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", "Makefile")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), os.path.join(dirpath, f)
+                assert "liboracle" not in text, os.path.join(dirpath, f)
+    _lib.build()
+    needed = subprocess.run(["objdump", "-p", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "NEEDED" in needed and "oracle" not in needed
