@@ -42,6 +42,17 @@ __global__ void max_f32(const float* __restrict__ X, int64_t n, float* __restric
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int*>(out), __float_as_int(m));
 }
 
+// ids of an imported COO must address the store: 0 <= id < V (one bad index from a host caller
+// would otherwise become an out-of-bounds device write in the update kernel)
+__global__ void check_ids(const int32_t* __restrict__ I, const int32_t* __restrict__ J, int64_t n, int32_t V,
+                          int32_t* __restrict__ bad) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    bool b = false;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride)
+        b |= (uint32_t)I[k] >= (uint32_t)V || (uint32_t)J[k] >= (uint32_t)V;
+    if (b) *bad = 1;
+}
+
 int check_csr(ge_ctx* ctx, int32_t V, const int64_t* off, const int32_t* nbr, const char* name) {
     if (off[0] != 0) { ctx->err = std::string(name) + "_off[0] != 0"; return GE_ERR_GRAPH; }
     for (int32_t v = 0; v < V; v++) {
@@ -118,6 +129,11 @@ extern "C" int ge_create(const ge_config* cfg, ge_ctx** out) {
     if (cfg->opt_method < GE_OPT_ADAGRAD || cfg->opt_method > GE_OPT_AMSGRAD) { g_create_err = "Invalid optimization method"; return GE_ERR_INVALID; }
     if (cfg->opt_method != GE_OPT_ADAGRAD && cfg->dim > 512) { g_create_err = "adam / amsgrad: dim must be <= 512"; return GE_ERR_INVALID; }
     if (cfg->normalize < 0 || cfg->normalize > 2) { g_create_err = "Invalid bca.normalize"; return GE_ERR_INVALID; }
+    if (cfg->update < GE_UPDATE_ATOMIC || cfg->update > GE_UPDATE_ATOMIC_ADAM) { g_create_err = "Invalid update mode"; return GE_ERR_INVALID; }
+    if (cfg->update == GE_UPDATE_ATOMIC_ADAM && cfg->opt_method == GE_OPT_ADAGRAD) {
+        g_create_err = "GE_UPDATE_ATOMIC_ADAM applies to adam / amsgrad only (adagrad: GE_UPDATE_ATOMIC)";
+        return GE_ERR_INVALID;
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         g_create_err = "no CUDA device: libgraphemb has no CPU fallback";
@@ -243,6 +259,7 @@ extern "C" int ge_cooc_stats(ge_ctx* ctx, int64_t* pops, int64_t* scanned, doubl
 extern "C" int ge_cooc_export(ge_ctx* ctx, int32_t* I, int32_t* J, float* X, int64_t cap) {
     if (!ctx) return GE_ERR_INVALID;
     if (!ctx->have_cooc) { ctx->err = "no co-occurrence matrix"; return GE_ERR_STATE; }
+    if (!ctx->d_I) { ctx->err = "the COO arrays were released when the matrix was bucketed for the multi-GPU trainer"; return GE_ERR_STATE; }
     if (cap < ctx->nnz) { ctx->err = "export capacity too small"; return GE_ERR_INVALID; }
     cudaSetDevice(ctx->cfg.device);
     const size_t n = (size_t)ctx->nnz;
@@ -257,8 +274,9 @@ extern "C" int ge_cooc_import(ge_ctx* ctx, int32_t V, int64_t nnz, const int32_t
                               const float* X, double xmax) {
     if (!ctx) return GE_ERR_INVALID;
     if (V <= 0 || nnz <= 0 || !I || !J || !X) { ctx->err = "bad matrix arguments"; return GE_ERR_INVALID; }
+    if (V > GE_ID_MASK) { ctx->err = "vocabulary must stay below 2^27 vertices (packed nonzero ids)"; return GE_ERR_INVALID; }
     cudaSetDevice(ctx->cfg.device);
-    if (ctx->V != V) ge_free_store(ctx);
+    if (ctx->V != V) { ge_free_store(ctx); ge_free_graph(ctx); }  // a resident graph of another V must not be walked with this V
     ge_free_cooc(ctx);
     ctx->V = V;
     const size_t n = (size_t)nnz;
@@ -268,6 +286,25 @@ extern "C" int ge_cooc_import(ge_ctx* ctx, int32_t V, int64_t nnz, const int32_t
     GE_CUDA(cudaMemcpyAsync(ctx->d_I, I, n * 4, cudaMemcpyHostToDevice, ctx->stream));
     GE_CUDA(cudaMemcpyAsync(ctx->d_J, J, n * 4, cudaMemcpyHostToDevice, ctx->stream));
     GE_CUDA(cudaMemcpyAsync(ctx->d_X, X, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    {
+        int32_t* d_bad = nullptr;
+        int32_t bad = 0;
+        GE_CUDA(cudaMalloc(&d_bad, 4));
+        cudaError_t e = cudaMemsetAsync(d_bad, 0, 4, ctx->stream);
+        if (e == cudaSuccess) {
+            check_ids<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, nnz, V, d_bad);
+            e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ctx->stream);
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_bad);
+        if (e != cudaSuccess || bad) {
+            cudaFree(ctx->d_I); cudaFree(ctx->d_J); cudaFree(ctx->d_X);
+            ctx->d_I = ctx->d_J = nullptr; ctx->d_X = nullptr;
+            GE_CUDA(e);
+            ctx->err = "matrix index out of range: every I/J must satisfy 0 <= id < V";
+            return GE_ERR_INVALID;
+        }
+    }
     ctx->nnz = nnz;
     if (xmax > 0) ctx->xmax = xmax;
     else {

@@ -48,6 +48,7 @@ struct BcaParams {
     // tier-2 scratch (global), per warp: laid out by the kernel from this base
     uint8_t* scratch;
     size_t scratch_per_warp;
+    int32_t ntables;                 // tier 2: tables in `scratch`; warps beyond it do nothing
     // outputs
     int32_t *aI, *aJ;
     float* aX;
@@ -206,6 +207,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
             p = smem + (size_t)wib * ((per + 15) & ~(size_t)15);
         } else {
             const size_t gw = (size_t)blockIdx.x * (blockDim.x >> 5) + wib;
+            if (gw >= (size_t)P.ntables) return;  // grid rounds up to whole blocks: no table behind this warp
             p = P.scratch + gw * P.scratch_per_warp;
         }
         T.wet = reinterpret_cast<double*>(p); p += (size_t)P.cap * 8;
@@ -470,8 +472,10 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
         AS.I[round] = (int32_t*)aI; AS.J[round] = (int32_t*)aJ; AS.X[round] = (float*)aX;
         P.aI = (int32_t*)aI; P.aJ = (int32_t*)aJ; P.aX = (float*)aX;
         P.arena_cap = arena_cap; P.arena_base = (int64_t)round * arena_cap;
-        cudaMemsetAsync(d32, 0, 12, st);   // next, n_overflow, n_deferred
-        cudaMemsetAsync(P.cursor, 0, 8, st);
+        if (cudaMemsetAsync(d32, 0, 12, st) != cudaSuccess ||   // next, n_overflow, n_deferred
+            cudaMemsetAsync(P.cursor, 0, 8, st) != cudaSuccess) {
+            ctx->err = std::string("bca round reset: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
+        }
         P.work = round == 0 ? nullptr : work.as<int32_t>();
         P.nwork = nwork;
         // ---- tier 1: shared-memory tables
@@ -502,12 +506,14 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
             if (cudaMalloc(&scratch.p, (size_t)warps * per2) != cudaSuccess || cudaMalloc(&list.p, (size_t)n_over * 4) != cudaSuccess) {
                 cudaGetLastError(); ctx->err = "out of device memory for tier-2 BCA tables"; rc = GE_ERR_NOMEM; break;
             }
-            cudaMemcpyAsync(list.p, P.overflow, (size_t)n_over * 4, cudaMemcpyDeviceToDevice, st);
-            cudaMemsetAsync(d32, 0, 8, st);  // next, n_overflow (n_deferred keeps counting)
+            if (cudaMemcpyAsync(list.p, P.overflow, (size_t)n_over * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess ||
+                cudaMemsetAsync(d32, 0, 8, st) != cudaSuccess) {  // next, n_overflow (n_deferred keeps counting)
+                ctx->err = std::string("bca tier-2 set-up: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
+            }
             BcaParams Q = P;
             Q.work = list.as<int32_t>(); Q.nwork = n_over;
             Q.cap = (int32_t)cap2; Q.hcap_log2 = hl;
-            Q.scratch = scratch.as<uint8_t>(); Q.scratch_per_warp = per2;
+            Q.scratch = scratch.as<uint8_t>(); Q.scratch_per_warp = per2; Q.ntables = (int32_t)warps;
             const int64_t blocks = (warps + T1_WARPS - 1) / T1_WARPS;
             bca_push<uint32_t, false><<<(unsigned)blocks, T1_WARPS * 32, 0, st>>>(Q);
             if (cudaMemcpyAsync(h, d32, 12, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
@@ -518,7 +524,9 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
         const int32_t n_def = h[2];
         if (n_def > 0) {
             if (!work.p && cudaMalloc(&work.p, (size_t)count * 4) != cudaSuccess) { cudaGetLastError(); rc = GE_ERR_NOMEM; ctx->err = "out of device memory"; break; }
-            cudaMemcpyAsync(work.p, P.deferred, (size_t)n_def * 4, cudaMemcpyDeviceToDevice, st);
+            if (cudaMemcpyAsync(work.p, P.deferred, (size_t)n_def * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+                ctx->err = std::string("bca deferred list: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
+            }
         }
         nwork = n_def;
     }

@@ -825,6 +825,7 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
 
 int ge_train_prepare(ge_ctx* ctx) {
     if (!ctx->have_cooc || ctx->nnz <= 0) { ctx->err = "no co-occurrence matrix: build or import one first"; return GE_ERR_STATE; }
+    if (!ctx->d_nz && !ctx->d_I) { ctx->err = "the COO arrays were released by ge_dist_prepare: use ge_dist_train_epoch"; return GE_ERR_STATE; }
     if (!ctx->have_store) { int r = ge_store_init(ctx); if (r) return r; }
     const ge_config& c = ctx->cfg;
     if (!ctx->d_nz) {
