@@ -1,7 +1,13 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c4|c3|c1|small]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c4|c3|c1|c2|c5|small]
+
+--workload c1 = BASELINE configs[0]: configs/dblp.config.yml (pglove, d=300 as shipped; --dim 100 for the
+d=100 override) on the DBLP-shaped synthetic graph, with a `parity` block (GPU loss curve and top-10
+neighbours against the committed single-thread oracle trajectory, tests/golden/parity_c1_*.npz) and the
+CPU port timed on the FULL matrix.  --workload c2 = configs[1]: onstage / saa pipelines, co-occurrence
+bit-exactness against the oracle build at full configured size.
 
 A *step* is one GloVe/AdaGrad epoch over all co-occurrence nonzeros of the workload graph
 (the matrix is built once, before the timed region, by the CUDA BCA builder and reported in
@@ -32,6 +38,9 @@ WORKLOADS = {
     # configs[4]: direct COO, multi-GPU only (store 243 GB at d=300); "E" = nonzeros at 8 GPUs
     "c5": (50_000_000, 1_000_000_000, 300, "synthetic COO 50M rows / 1e9 nonzeros, d=300 (BASELINE configs[4])"),
     "small": (200_000, 2_000_000, 128, "R-MAT 200k nodes / 2M edges, d=128 (smoke-sized)"),
+    # configs[0] / configs[1]: graphs come from synth.dblp_like / onstage_like / saa_like, see run_c1 / run_c2
+    "c1": (320_000, 1_000_000, 300, "configs/dblp.config.yml on the DBLP-shaped synthetic graph (BASELINE configs[0])"),
+    "c2": (0, 0, 300, "configs/onstage.config.yml + saa.config.yml on graphs of their shape (BASELINE configs[1])"),
 }
 ALPHA, EPS, SEED = 0.1, 1e-3, 5
 
@@ -163,6 +172,188 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _topk_gpu(E, sample, k=10):
+    import torch
+    E = torch.as_tensor(np.asarray(E, np.float32), device="cuda")
+    En = E / E.norm(dim=1, keepdim=True).clamp_min(1e-12)
+    s = torch.as_tensor(np.asarray(sample, np.int64), device="cuda")
+    out = []
+    for a in range(0, len(s), 2000):
+        rows = s[a:a + 2000]
+        S = En[rows] @ En.T
+        S[torch.arange(len(rows), device="cuda"), rows] = -float("inf")
+        out.append(S.topk(k, dim=1).indices.to(torch.int32).cpu())
+    return torch.cat(out).numpy()
+
+
+def _coo_checksums(I, J, X):
+    """order-independent checksums, as tests/golden/make_parity_curves.py computes them"""
+    xb = X.view(np.uint32).astype(np.uint64)
+    k = (I.astype(np.uint64) << np.uint64(32)) | J.astype(np.uint64)
+    with np.errstate(over="ignore"):
+        mixed = (k * np.uint64(0x9E3779B97F4A7C15)) ^ xb
+        return np.array([len(I), int(xb.sum(dtype=np.uint64)), int(mixed.sum(dtype=np.uint64))], np.uint64)
+
+
+def run_c1(args):
+    """BASELINE configs[0]: dblp.config.yml as shipped (pglove, d=300) or --dim 100, on the DBLP-shaped
+    graph; CPU path (oracle port, full matrix) then 1 B200; parity block against the committed
+    single-thread trajectory."""
+    import torch
+    from graph_embeddings_b200 import BookmarkColoring, ImportedMatrix, createOptimizer, synth
+    from graph_embeddings_b200.config import load_config
+    torch.cuda.set_device(0)
+    K, W = args.steps, args.warmup
+    cfg = load_config(os.path.join(ROOT, "configs", "dblp.config.yml"), check=False, seed=31)
+    if args.dim:
+        cfg.dim = args.dim
+    dim = cfg.dim
+    cfg.opt.tolerance, cfg.opt.maxiter = 0.0, K             # fixed K epochs: a step is one epoch
+    g = synth.dblp_like(1.0, 1)
+    peak, peak_src = peaks()
+
+    # ---- e2e through the public API from host buffers
+    torch.cuda.synchronize()
+    t0 = time.time()
+    bca = BookmarkColoring(g, cfg)
+    opt = createOptimizer(cfg, bca)
+    e2e_costs = [opt.epoch() for _ in range(K)]
+    emb = opt.extractResult()                                # what the seam returns: double[V*dim]
+    torch.cuda.synchronize()
+    t_e2e = time.time() - t0
+    nnz, cst = bca.coOccurrenceCount(), bca.stats()
+    h2d = g.out_off.nbytes * 2 + g.out_nbr.nbytes * 2 + g.out_w.nbytes * 2
+    d2h = emb.nbytes + 8 * K
+    I, J, X = bca.coo()
+
+    # ---- parity: the throughput path from the fixture's init, per-epoch loss + top-10 neighbours
+    parity = None
+    fx = os.path.join(ROOT, "tests", "golden", f"parity_c1_pglove_d{dim}.npz")
+    if os.path.exists(fx):
+        F = np.load(fx)
+        ne = int(F["epochs"])
+        c2 = load_config(os.path.join(ROOT, "configs", "dblp.config.yml"), check=False, seed=int(F["seed"]))
+        c2.dim, c2.opt.tolerance, c2.opt.maxiter = dim, 0.0, ne
+        o2 = createOptimizer(c2, ImportedMatrix(g.V, I, J, X, c2, xmax=bca.max()))
+        hist = np.array([o2.epoch() for _ in range(ne)])
+        nn = _topk_gpu(o2.extractResultF32(), F["sample"])
+        del o2
+        ref = F["hist_exact"]
+        rel = np.abs(hist - ref) / ref
+        parity = {"fixture": os.path.basename(fx), "epochs": ne, "loss_gpu": hist.tolist(), "loss_oracle_1thread": ref.tolist(),
+                  "max_rel_loss_diff": float(rel.max()),
+                  "loss_oracle_f32_running_sum": F["hist"].tolist(),
+                  "note": "oracle = C++ restatement, 1 thread, reference epoch order; loss_oracle_1thread sums the epoch cost in "
+                          "fp64, loss_oracle_f32_running_sum is what Adagrad.java:60's float accumulator reports for the same run",
+                  "self_overlap_oracle_other_order": float(F["self_ov"])}
+        parity["top10_overlap"] = float(np.mean([len(set(a) & set(b)) / 10 for a, b in zip(nn, F["nn"])]))
+        parity["coo_checksum_matches_fixture"] = bool(np.array_equal(_coo_checksums(I, J, X), F["coo"]))
+
+    # ---- device-timed region
+    bca._n.set_stream(torch.cuda.current_stream().cuda_stream)
+    for _ in range(W):
+        opt.epoch()
+    s0 = opt.stats()
+    clocks = ClockSampler(0).start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    costs = [opt.epoch() for _ in range(K)]
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop()
+    s1 = opt.stats()
+    kern_s = (s1["update_seconds"] - s0["update_seconds"]) / K
+    B = 32 * dim + 44
+    achieved = nnz * B / kern_s / 1e9
+
+    # ---- CPU port on the FULL matrix: nproc-1 Hogwild threads (the reference default) and, on request, 1 thread
+    cb = None
+    if not args.no_cpu_baseline:
+        import oracle
+        threads = max(1, (os.cpu_count() or 2) - 1)
+        t1 = time.time()
+        c = oracle.cooc_build(g, ALPHA, EPS, True, "none", threads=threads)
+        build_s = time.time() - t1
+        assert c.nnz == nnz
+        tr = oracle.Trainer(g.V, c.I, c.J, c.X, c.max, dim, cfg.method, 31, threads=threads)
+        tr.epoch()
+        t2 = time.time()
+        ne = 2
+        for _ in range(ne):
+            tr.epoch()
+        dt = (time.time() - t2) / ne
+        tr.close()
+        cb = {"value": nnz / dt, "unit": "nnz_updates/s", "cores": threads, "kind": "port",
+              "sample": f"FULL matrix ({nnz} nonzeros), {ne} timed epochs after 1 warm-up, C++ restatement, Hogwild threads={threads}",
+              "ms_per_step": dt * 1e3, "cooc_pairs_per_s": c.pops / build_s, "cooc_build_seconds": build_s}
+        if args.cpu_1thread:
+            tr = oracle.Trainer(g.V, c.I, c.J, c.X, c.max, dim, cfg.method, 31, threads=1)
+            t2 = time.time()
+            tr.epoch()
+            d1 = time.time() - t2
+            tr.close()
+            cb["one_thread"] = {"value": nnz / d1, "ms_per_step": d1 * 1e3, "sample": "FULL matrix, 1 epoch, 1 thread (the parity trajectory)"}
+    line = {"metric": "glove_nnz_updates_per_sec", "value": nnz * K / (ms * 1e-3), "unit": "nnz_updates/s", "n_gpus": 1,
+            "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOADS["c1"][3], "config_file": "configs/dblp.config.yml", "V": g.V, "E": g.E, "nnz": nnz,
+                       "dim": dim, "alpha": cfg.bca.alpha, "epsilon": cfg.bca.epsilon, "method": cfg.method, "optimizer": cfg.opt.method,
+                       "math": "f32 fast path, atomic red.add row updates", "order": cfg.order,
+                       "l2": "store %.2f GB + nonzeros %.2f GB: larger than L2" % (2 * g.V * ((2 * ((dim + 3) // 4 * 4) + 9) // 8 * 8) * 4 / 1e9, nnz * 16 / 1e9),
+                       "final_cost": costs[-1]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "glove_adagrad_update", "bytes_per_nnz": B, "peak_source": peak_src, "kernel_ms": kern_s * 1e3},
+            "cooc": {"pairs_per_s": cst["pops"] / cst["seconds"], "nnz_per_s": nnz / cst["seconds"], "seconds": cst["seconds"],
+                     "pops": cst["pops"], "scanned": cst["scanned"]},
+            "parity": parity,
+            "e2e": {"value": nnz * K / t_e2e, "unit": "nnz_updates/s", "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+                    "seconds": t_e2e, "includes": "graph hand-off H2D, BCA build, store init, K epochs with loss read-back, f64 result D2H"},
+            "gpu_launches": int(s1["launches"] - s0["launches"]), "clocks": clk}
+    if cb:
+        line["cpu_baseline"] = cb
+    print(json.dumps(line), flush=True)
+
+
+def run_c2(args):
+    """BASELINE configs[1]: onstage / saa pipelines on graphs of their configured shape, 1 B200:
+    co-occurrence bit-exactness against the oracle build (all host threads), pairs/s both sides."""
+    import torch
+    import oracle
+    from graph_embeddings_b200 import BookmarkColoring, synth
+    from graph_embeddings_b200.config import load_config
+    torch.cuda.set_device(0)
+    threads = max(1, (os.cpu_count() or 2) - 1)
+    res, tot_pops, tot_s, tot_cpu_s = {}, 0, 0.0, 0.0
+    for name, g in (("onstage", synth.onstage_like(1.0, 2)), ("saa", synth.saa_like(1.0, 3))):
+        cfg = load_config(os.path.join(ROOT, "configs", f"{name}.config.yml"), check=False, seed=31)
+        for _ in range(max(1, args.warmup)):
+            bca = BookmarkColoring(g, cfg)
+        st = bca.stats()
+        I, J, X = bca.coo()
+        t0 = time.time()
+        ref = oracle.cooc_build(g, cfg.bca.alpha, cfg.bca.epsilon, True, "none", threads=threads)
+        cpu_s = time.time() - t0
+        o = np.lexsort((J, I))
+        ri, rj, rx = ref.sorted()
+        exact = bool(bca.coOccurrenceCount() == ref.nnz and np.array_equal(I[o], ri) and np.array_equal(J[o], rj)
+                     and np.array_equal(X[o].view(np.uint32), rx.view(np.uint32)) and bca.max() == ref.max)
+        res[name] = {"V": g.V, "E": g.E, "nnz": int(ref.nnz), "bit_exact": exact, "gpu_seconds": st["seconds"],
+                     "gpu_pairs_per_s": st["pops"] / st["seconds"], "cpu_seconds": cpu_s, "cpu_pairs_per_s": ref.pops / cpu_s,
+                     "pops": int(st["pops"]), "pops_match": bool(st["pops"] == ref.pops), "xmax": bca.max()}
+        tot_pops += st["pops"]; tot_s += st["seconds"]; tot_cpu_s += cpu_s
+        del bca
+    line = {"metric": "cooc_pairs_per_sec", "value": tot_pops / tot_s, "unit": "pairs/s", "n_gpus": 1, "steps": 1, "warmup": args.warmup,
+            "ms_per_step": tot_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 paint / f32 sums",
+            "data": "synthetic", "config": {"workload": WORKLOADS["c2"][3], "graphs": res},
+            "parity": {"bit_exact": all(r["bit_exact"] for r in res.values()), "oracle": "C++ restatement, all host threads"},
+            "cpu_baseline": {"value": tot_pops / tot_cpu_s, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": "FULL graphs"},
+            "gpu_launches": 2}
+    print(json.dumps(line), flush=True)
+
+
+
 def run_single(args):
     import torch
     from graph_embeddings_b200 import BCA, BookmarkColoring, Configuration, Opt, createOptimizer
@@ -264,7 +455,13 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default=os.environ.get("GE_BENCH_WORKLOAD", "c4"), choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dim", type=int, default=0, help="c1: override dblp.config.yml's dim (BASELINE configs[0]: d=100)")
+    ap.add_argument("--cpu-1thread", action="store_true", help="c1: also time one full single-thread epoch of the CPU port")
     args = ap.parse_args()
+    if args.workload == "c1" and args.impl != "reference":
+        return run_c1(args)
+    if args.workload == "c2" and args.impl != "reference":
+        return run_c2(args)
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))

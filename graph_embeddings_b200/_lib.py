@@ -91,6 +91,7 @@ SIGNATURES = {
     "ge_dist_train_epoch": (C.c_int, [_P, C.POINTER(_F64)]),
     "ge_dist_extract_f32": (C.c_int, [_P, _P, _I64]),
     "ge_dist_stats": (C.c_int, [_P, _P, _I32, C.POINTER(_F64), C.POINTER(_I64)]),
+    "ge_dist_rotation_mode": (C.c_int, [_P]),
 }
 
 

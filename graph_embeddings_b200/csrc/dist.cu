@@ -14,10 +14,22 @@
 //
 // Replaces the reference's thread slicing of the shuffled nonzeros (J/opt/Optimizer.java:59-63,
 // J/opt/grad/Adagrad.java:47-49), which has no multi-device counterpart.
+//
+// Rotation data plane (world > 1), default GE_DIST_ROT=ce: every column block is cut in two
+// halves; as soon as the update of the window's first block has finished a half, that half is
+// pushed into the neighbour's spare ring slot by the COPY ENGINE (cudaMemcpyAsync on a peer
+// mapping obtained through CUDA IPC, no SMs involved) while the SMs update the other half / the
+// other window blocks.  Hand-shake = two flag words per half in each rank's memory, written by the
+// neighbours' copy streams with 4-byte DMA copies and awaited with stream memory operations
+// (cuStreamWaitValue32): `ready` (rank+1 -> me: half p of transfer q has landed) and `free`
+// (rank-1 -> me: the half-slot I am about to overwrite has been sent on).  GE_DIST_ROT=nccl keeps
+// the round-1 plane (whole block, ncclSend/ncclRecv in the compute stream), GE_DIST_ROT=pipe the
+// half-block NCCL variant.
 #include "common.cuh"
 
 #include <dlfcn.h>
 
+#include <cstdio>
 #include <cstring>
 
 namespace {
@@ -34,6 +46,8 @@ struct NcclApi {
     int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
@@ -45,6 +59,7 @@ struct NcclApi {
 #define SYM(f, s) f = reinterpret_cast<decltype(f)>(dlsym(h, s)); if (!f) { err = std::string("libnccl lacks ") + s; return false; }
         SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
         SYM(Send, "ncclSend") SYM(Recv, "ncclRecv") SYM(AllReduce, "ncclAllReduce")
+        SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast")
         SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd") SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
         return true;
@@ -53,6 +68,10 @@ struct NcclApi {
 NcclApi g_nccl;
 
 }  // namespace
+
+enum { ROT_NCCL = 0, ROT_PIPE = 1, ROT_CE = 2 };
+constexpr uint32_t SEQTAB = 1u << 20;   // sub-epochs a prepared trainer can run (131 072 epochs of 8)
+typedef int (*WaitValue32Fn)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
 
 struct DistState {
     int rank = 0, world = 1;
@@ -73,6 +92,16 @@ struct DistState {
     int head = 0;                     // slot of the window's first block
     int sub = 0;                      // sub-epochs done in the current rotation (block ids derive from it)
     double comm_seconds = 0;
+    // --- copy-engine rotation (GE_DIST_ROT=ce) ---
+    int rot = ROT_NCCL;               // data plane in use
+    float* peer_ring = nullptr;       // rank-1's ring allocation, mapped through CUDA IPC
+    float* next_ring = nullptr;       // rank+1's ring allocation (only its flag words are written); == peer_ring when world == 2
+    uint32_t* flags = nullptr;        // local flag words, in the tail of the ring allocation: ready[0..1], free[2..3]
+    uint32_t* prev_flags = nullptr;   // rank-1's flags (I write its ready[p])
+    uint32_t* next_flags = nullptr;   // rank+1's flags (I write its free[p])
+    uint32_t* seqtab = nullptr;       // seqtab[k] = k: source of the 4-byte flag copies
+    uint32_t q = 0;                   // transfers issued per half so far (= sub-epochs done)
+    std::vector<cudaEvent_t> xfer_ev; // 2 events per transfer of an epoch (copy alone, no waits)
     std::vector<int32_t> bucket_hot;  // bucket has entries with damping exponents -> HOT kernel variant
     cudaEvent_t c0 = nullptr, c1 = nullptr;
 };
@@ -83,6 +112,10 @@ void ge_dist_free(ge_ctx* ctx) {
     cudaFree(d->d_nzb);
     cudaFree(d->d_Cring);
     cudaFree(d->d_queue);
+    if (d->next_ring && d->next_ring != d->peer_ring) cudaIpcCloseMemHandle(d->next_ring);
+    if (d->peer_ring) cudaIpcCloseMemHandle(d->peer_ring);
+    cudaFree(d->seqtab);
+    for (cudaEvent_t e : d->xfer_ev) cudaEventDestroy(e);
     for (int p = 0; p < 2; p++) { if (d->ev_done[p]) cudaEventDestroy(d->ev_done[p]); if (d->ev_recv[p]) cudaEventDestroy(d->ev_recv[p]); }
     if (d->cs) cudaStreamDestroy(d->cs);
     if (d->c0) cudaEventDestroy(d->c0);
@@ -169,6 +202,100 @@ __global__ void dist_extract(const float* __restrict__ W, const float* __restric
 }  // namespace
 
 
+
+namespace {
+
+struct IpcPair { cudaIpcMemHandle_t ring; int32_t ok; int32_t pad[15]; };
+
+void dist_unmap_peers(DistState* d) {
+    if (d->next_ring && d->next_ring != d->peer_ring) cudaIpcCloseMemHandle(d->next_ring);
+    if (d->peer_ring) cudaIpcCloseMemHandle(d->peer_ring);
+    d->peer_ring = d->next_ring = nullptr;
+    d->prev_flags = d->next_flags = nullptr;
+}
+
+WaitValue32Fn g_wait32 = nullptr;
+
+// Exchange CUDA IPC handles of every rank's ring and flag words (one ncclAllGather) and map the
+// neighbours'.  Falls back to the NCCL plane when IPC or stream memory operations are unavailable.
+int dist_map_peers(ge_ctx* ctx) {
+    DistState* d = ctx->dist;
+    cudaStream_t st = ctx->stream;
+    dist_unmap_peers(d);
+    if (!d->seqtab) {
+        GE_CUDA(cudaMalloc(&d->seqtab, (size_t)SEQTAB * 4));
+        std::vector<uint32_t> h(SEQTAB);
+        for (uint32_t k = 0; k < SEQTAB; k++) h[k] = k;
+        GE_CUDA(cudaMemcpyAsync(d->seqtab, h.data(), (size_t)SEQTAB * 4, cudaMemcpyHostToDevice, st));
+        GE_CUDA(cudaStreamSynchronize(st));
+    }
+    d->q = 0;
+    bool ok = true;
+    if (!g_wait32) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) { cudaGetLastError(); ok = false; }
+        else g_wait32 = reinterpret_cast<WaitValue32Fn>(fn);
+    }
+    IpcPair mine{};
+    if (ok && cudaIpcGetMemHandle(&mine.ring, d->d_Cring) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    mine.ok = ok ? 1 : 0;
+    // every rank takes part in the gather even when its own set-up failed
+    IpcPair* d_all = nullptr;
+    GE_CUDA(cudaMalloc(&d_all, sizeof(IpcPair) * (size_t)(d->world + 1)));
+    std::vector<IpcPair> all(d->world);
+    cudaError_t e = cudaMemcpyAsync(d_all + d->world, &mine, sizeof(IpcPair), cudaMemcpyHostToDevice, st);
+    int nr = 0;
+    if (e == cudaSuccess) nr = g_nccl.AllGather(d_all + d->world, d_all, sizeof(IpcPair), NCCL_UINT8, d->comm, st);
+    if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(all.data(), d_all, sizeof(IpcPair) * (size_t)d->world, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
+    cudaFree(d_all);
+    GE_CUDA(e);
+    GE_NCCL(nr);
+    for (int k = 0; k < d->world; k++) ok = ok && all[k].ok == 1;
+    const int prev = (d->rank + d->world - 1) % d->world, next = (d->rank + 1) % d->world;
+    if (ok) {
+        // the flag words sit behind the last slot of every ring allocation (same geometry on all ranks)
+        const size_t ring_floats = (size_t)(d->m + 1) * d->Bs * ctx->S;
+        void *pr = nullptr, *nr2 = nullptr;
+        if (cudaIpcOpenMemHandle(&pr, all[prev].ring, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
+        if (ok && next != prev && cudaIpcOpenMemHandle(&nr2, all[next].ring, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = false;
+        if (!ok) {
+            cudaGetLastError();
+            if (pr) cudaIpcCloseMemHandle(pr);
+        } else {
+            d->peer_ring = (float*)pr;
+            d->next_ring = next != prev ? (float*)nr2 : (float*)pr;
+            d->prev_flags = reinterpret_cast<uint32_t*>(d->peer_ring + ring_floats);
+            d->next_flags = reinterpret_cast<uint32_t*>(d->next_ring + ring_floats);
+        }
+    }
+    // agree on the plane: one rank that could not map its neighbour sends everybody to NCCL
+    {
+        double* d_ok = nullptr;
+        GE_CUDA(cudaMalloc(&d_ok, 8));
+        double hv = ok ? 0.0 : 1.0;
+        e = cudaMemcpyAsync(d_ok, &hv, 8, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) nr = g_nccl.AllReduce(d_ok, d_ok, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st);
+        if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(&hv, d_ok, 8, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
+        cudaFree(d_ok);
+        GE_CUDA(e);
+        GE_NCCL(nr);
+        if (hv != 0.0) {
+            if (getenv("GE_DEBUG")) fprintf(stderr, "[graphemb] rank %d: CUDA IPC / stream memory operations unavailable, rotation falls back to NCCL send/recv\n", d->rank);
+            d->rot = ROT_PIPE;
+        }
+    }
+    if (d->rot == ROT_CE && d->xfer_ev.empty()) {
+        d->xfer_ev.resize((size_t)4 * d->nb);
+        for (auto& ev : d->xfer_ev) GE_CUDA(cudaEventCreate(&ev));
+    }
+    return GE_OK;
+}
+
+}  // namespace
+
 extern "C" int ge_dist_unique_id(void* id128) {
     std::string err;
     if (!id128 || !g_nccl.load(err)) return GE_ERR_DIST;
@@ -236,11 +363,17 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     }
     d->nb = nblocks; d->m = nblocks / d->world;
     d->Bs = (ctx->V + nblocks - 1) / nblocks;
-    // GE_DIST_PIPE=1: half-block rotation on a second stream behind the compute (measured on 2 B200s:
-    // C5 -5 %, C4 +6 % time: NCCL's copy CTAs cannot get SM slots beside the persistent update wave, so it
-    // stays opt-in; default = whole-block rotation on the compute stream)
-    static const bool pipe = getenv("GE_DIST_PIPE") && atoi(getenv("GE_DIST_PIPE")) == 1;
-    d->P = (d->world > 1 && pipe) ? 2 : 1;
+    // data plane of the rotation (see the file header).  Half blocks (P = 2) for every world size,
+    // so that a 1-GPU run of the schedule walks exactly the buckets (and per-bucket order keys) of
+    // an N-GPU run: that is what the N-rank-vs-1-rank loss check compares.
+    {
+        const char* e = getenv("GE_DIST_ROT");
+        const char* legacy = getenv("GE_DIST_PIPE");
+        d->rot = ROT_CE;
+        if (e && !strcmp(e, "nccl")) d->rot = ROT_NCCL;
+        else if ((e && !strcmp(e, "pipe")) || (!e && legacy && atoi(legacy) == 1)) d->rot = ROT_PIPE;
+    }
+    d->P = d->rot == ROT_NCCL ? 1 : 2;
     d->Hs = d->P > 1 ? (d->Bs + 1) / 2 : d->Bs;
     if (d->m * d->nb * d->P > 1024) { ctx->err = "too many buckets (nblocks^2 / world * 2 must be <= 1024)"; return GE_ERR_INVALID; }
     d->row_base = first; d->row_cnt = count;
@@ -306,20 +439,35 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     ctx->d_I = ctx->d_J = nullptr; ctx->d_X = nullptr;
 
     // ---- store: W rows of this rank, ring of C block slots
+    if (d->world > 1 && d->peer_ring) {
+        // re-prepare: nobody may free a ring a neighbour still has mapped -> unmap, then a barrier
+        dist_unmap_peers(d);
+        double* d_b = nullptr;
+        GE_CUDA(cudaMalloc(&d_b, 8));
+        GE_CUDA(cudaMemsetAsync(d_b, 0, 8, st));
+        GE_NCCL(g_nccl.AllReduce(d_b, d_b, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st));
+        GE_CUDA(cudaStreamSynchronize(st));
+        cudaFree(d_b);
+    }
     ge_free_store(ctx);
     ge_store_geometry(ctx);
     const size_t slab = (size_t)d->Bs * ctx->S;  // floats per block
     const int slots = d->world > 1 ? d->m + 1 : d->m;
     GE_CUDA(cudaMalloc(&ctx->d_W, (size_t)d->m * slab * sizeof(float)));
     cudaFree(d->d_Cring); d->d_Cring = nullptr;
-    GE_CUDA(cudaMalloc(&d->d_Cring, (size_t)slots * slab * sizeof(float)));
+    GE_CUDA(cudaMalloc(&d->d_Cring, (size_t)slots * slab * sizeof(float) + 256));  // + the rotation's flag words
+    d->flags = reinterpret_cast<uint32_t*>(d->d_Cring + (size_t)slots * slab);
     GE_CUDA(cudaMemsetAsync(ctx->d_W, 0, (size_t)d->m * slab * sizeof(float), st));
-    GE_CUDA(cudaMemsetAsync(d->d_Cring, 0, (size_t)slots * slab * sizeof(float), st));
+    GE_CUDA(cudaMemsetAsync(d->d_Cring, 0, (size_t)slots * slab * sizeof(float) + 256, st));
     r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, count, first);
     if (r) return r;
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
     cudaFree(d->d_queue); d->d_queue = nullptr;
     GE_CUDA(cudaMalloc(&d->d_queue, (size_t)nbuckets * sizeof(unsigned long long)));
+    if (d->world > 1 && d->rot == ROT_CE) {
+        r = dist_map_peers(ctx);
+        if (r) return r;
+    }
     d->head = 0; d->sub = 0;
     ctx->epoch = 0;
     ctx->history.clear();
@@ -339,21 +487,22 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     uint64_t ekey = (uint64_t)c.seed * 0x9E3779B97F4A7C15ULL + (uint64_t)(ctx->epoch + 1) * 0xD6E8FEB86659FD93ULL;
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), st));
     GE_CUDA(cudaEventRecord(ctx->ev0, st));
-    float comm_ms = 0;
     const int P = d->P;
-    const bool piped = d->world > 1 && P > 1;
+    const int rot = d->world > 1 ? d->rot : -1;
+    const bool piped = rot == ROT_PIPE;
+    if (rot == ROT_CE && (uint64_t)d->q + (uint64_t)d->nb + 1 >= SEQTAB) { ctx->err = "rotation sequence table exhausted: ge_dist_prepare again"; return GE_ERR_STATE; }
     if (piped) GE_CUDA(cudaMemsetAsync(d->d_queue, 0, (size_t)d->m * d->nb * P * sizeof(unsigned long long), st));
     // byte ranges of the P parts of a block slab (part 0 = rows [0, Hs), part 1 = rows [Hs, Bs))
     const size_t part_off[2] = {0, (size_t)d->Hs * ctx->S};
     const size_t part_len[2] = {(size_t)d->Hs * ctx->S, (size_t)(d->Bs - d->Hs) * ctx->S};
     const int to = (d->rank + d->world - 1) % d->world, from = (d->rank + 1) % d->world;
+    int nxfer = 0;
     for (int s = 0; s < d->nb; s++) {
         // window of C blocks held now: block (rank*m + s + k) mod nb sits in slot (head + k) mod slots.
-        // Pipelined rotation (world > 1): the window's FIRST block is updated first, part by part; as
-        // soon as a part is done it leaves for rank-1 on the copy stream while the next part / the
-        // other window blocks are being updated, and the matching part of the block arriving from
-        // rank+1 lands in the spare slot.  That block is the window's LAST one in the next sub-epoch,
-        // whose updates wait on the part's arrival only.
+        // The window's FIRST block is updated first, part by part; as soon as a part is done it leaves
+        // for rank-1 while the next part / the other window blocks are being updated, and the matching
+        // part of the block arriving from rank+1 lands in the spare slot.  That block is the window's
+        // LAST one in the next sub-epoch, whose updates wait on the part's arrival only.
         for (int k = 0; k < d->m; k++) {
             const int cb = (d->rank * d->m + s + k) % d->nb;
             const int lrb = k;  // virtual rank v = rank*m + k processes column block (v + s) mod nb
@@ -361,40 +510,60 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
             for (int p = 0; p < P; p++) {
                 const int bucket = (lrb * d->nb + cb) * P + p;
                 const int64_t off = d->bucket_off[bucket], cnt = d->bucket_off[bucket + 1] - off;
-                if (piped && k == d->m - 1 && s > 0) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));
+                if (k == d->m - 1 && d->q > 0) {  // this block arrived during the previous sub-epoch (transfer q-1)
+                    if (piped) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));
+                    else if (rot == ROT_CE && g_wait32(st, (unsigned long long)(uintptr_t)(d->flags + p), d->q, 0 /* GEQ */) != 0) {
+                        ctx->err = "cuStreamWaitValue32 (ready flag) failed"; return GE_ERR_CUDA;
+                    }
+                }
                 int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
                                          ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs,
                                          d->bucket_hot[bucket] != 0, piped ? d->d_queue + bucket : nullptr);
                 if (r) return r;
-                if (piped && k == 0) {
-                    float* sendp = d->d_Cring + (size_t)d->head * slab + part_off[p];
-                    float* recvp = d->d_Cring + (size_t)((d->head + d->m) % slots) * slab + part_off[p];
-                    GE_CUDA(cudaEventRecord(d->ev_done[p], st));
-                    GE_CUDA(cudaStreamWaitEvent(d->cs, d->ev_done[p], 0));
-                    const bool timed = s == d->nb - 1 && p == P - 1;
-                    if (timed) cudaEventRecord(d->c0, d->cs);
+                if (k != 0 || (!piped && rot != ROT_CE)) continue;
+                const size_t src_off = (size_t)d->head * slab + part_off[p];
+                const size_t dst_off = (size_t)((d->head + d->m) % slots) * slab + part_off[p];
+                GE_CUDA(cudaEventRecord(d->ev_done[p], st));
+                GE_CUDA(cudaStreamWaitEvent(d->cs, d->ev_done[p], 0));
+                if (piped) {
                     GE_NCCL(g_nccl.GroupStart());
-                    GE_NCCL(g_nccl.Send(sendp, part_len[p] * sizeof(float), NCCL_UINT8, to, d->comm, d->cs));
-                    GE_NCCL(g_nccl.Recv(recvp, part_len[p] * sizeof(float), NCCL_UINT8, from, d->comm, d->cs));
+                    GE_NCCL(g_nccl.Send(d->d_Cring + src_off, part_len[p] * sizeof(float), NCCL_UINT8, to, d->comm, d->cs));
+                    GE_NCCL(g_nccl.Recv(d->d_Cring + dst_off, part_len[p] * sizeof(float), NCCL_UINT8, from, d->comm, d->cs));
                     GE_NCCL(g_nccl.GroupEnd());
-                    if (timed) cudaEventRecord(d->c1, d->cs);
                     GE_CUDA(cudaEventRecord(d->ev_recv[p], d->cs));
+                } else {
+                    // transfer q, part p: my slot `head` -> rank-1's slot (head + m) % slots.  That slot is
+                    // the one rank-1 sent FROM in transfer q-1: wait until it says so (free >= q).
+                    if (g_wait32(d->cs, (unsigned long long)(uintptr_t)(d->flags + 2 + p), d->q, 0) != 0) {
+                        ctx->err = "cuStreamWaitValue32 (free flag) failed"; return GE_ERR_CUDA;
+                    }
+                    cudaEvent_t e0 = d->xfer_ev[(size_t)2 * nxfer], e1 = d->xfer_ev[(size_t)2 * nxfer + 1];
+                    nxfer++;
+                    GE_CUDA(cudaEventRecord(e0, d->cs));
+                    GE_CUDA(cudaMemcpyAsync(d->peer_ring + dst_off, d->d_Cring + src_off, part_len[p] * sizeof(float),
+                                            cudaMemcpyDeviceToDevice, d->cs));
+                    GE_CUDA(cudaEventRecord(e1, d->cs));
+                    // flags travel as 4-byte DMA copies behind the data on the same stream (no SM involved)
+                    GE_CUDA(cudaMemcpyAsync(d->prev_flags + p, d->seqtab + d->q + 1, 4, cudaMemcpyDeviceToDevice, d->cs));      // ready at rank-1
+                    GE_CUDA(cudaMemcpyAsync(d->next_flags + 2 + p, d->seqtab + d->q + 1, 4, cudaMemcpyDeviceToDevice, d->cs));  // free at rank+1
                 }
             }
         }
-        if (d->world > 1 && !piped) {  // GE_DIST_PIPE=0: whole-block rotation on the compute stream
+        if (rot == ROT_NCCL) {  // whole-block rotation on the compute stream
             float* sendp = d->d_Cring + (size_t)d->head * slab;
             float* recvp = d->d_Cring + (size_t)((d->head + d->m) % slots) * slab;
-            cudaEventRecord(d->c0, st);
             GE_NCCL(g_nccl.GroupStart());
             GE_NCCL(g_nccl.Send(sendp, slab * sizeof(float), NCCL_UINT8, to, d->comm, st));
             GE_NCCL(g_nccl.Recv(recvp, slab * sizeof(float), NCCL_UINT8, from, d->comm, st));
             GE_NCCL(g_nccl.GroupEnd());
-            cudaEventRecord(d->c1, st);
         }
         d->head = (d->head + 1) % slots;  // one GPU: the rotation is this pointer shift alone
+        if (d->world > 1) d->q++;
     }
-    if (piped) for (int p = 0; p < P; p++) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));  // every block home
+    // every block home before the epoch ends: the last transfer's parts have landed here
+    if (piped) for (int p = 0; p < P; p++) GE_CUDA(cudaStreamWaitEvent(st, d->ev_recv[p], 0));
+    if (rot == ROT_CE) for (int p = 0; p < P; p++)
+        if (g_wait32(st, (unsigned long long)(uintptr_t)(d->flags + p), d->q, 0) != 0) { ctx->err = "cuStreamWaitValue32 (epoch end) failed"; return GE_ERR_CUDA; }
     if (d->world == 1) d->head = (d->head + slots - (d->nb % slots)) % slots;  // nb shifts of an nb-ring: identity
     GE_CUDA(cudaEventRecord(ctx->ev1, st));
     double total = 0;
@@ -404,7 +573,13 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->update_seconds += ms * 1e-3;
-    if (d->world > 1) { cudaEventElapsedTime(&comm_ms, d->c0, d->c1); d->comm_seconds += comm_ms * 1e-3 * d->nb * d->P; }
+    if (rot == ROT_CE) {  // every transfer timed on the copy stream behind its waits: the DMA alone
+        GE_CUDA(cudaStreamSynchronize(d->cs));
+        for (int x = 0; x < nxfer; x++) {
+            float t = 0;
+            if (cudaEventElapsedTime(&t, d->xfer_ev[(size_t)2 * x], d->xfer_ev[(size_t)2 * x + 1]) == cudaSuccess) d->comm_seconds += t * 1e-3;
+        }
+    }
     const double local = total / (double)d->nnz_global;
     ctx->history.push_back(local);
     ctx->epoch++;
@@ -439,7 +614,16 @@ extern "C" int ge_dist_extract_f32(ge_ctx* ctx, float* out, int64_t cap) {
     return GE_OK;
 }
 
-// per-rank bookkeeping: nnz of each (local row-block, col-block) bucket, seconds in rotation
+// data plane of the rotation actually in use: 0 = NCCL send/recv in the compute stream, 1 = half-block
+// NCCL on a second stream, 2 = half blocks pushed by the copy engine into the neighbour's IPC-mapped
+// ring; -1 = single GPU (pointer shift)
+extern "C" int ge_dist_rotation_mode(ge_ctx* ctx) {
+    if (!ctx || !ctx->dist) return GE_ERR_STATE;
+    return ctx->dist->world > 1 ? ctx->dist->rot : -1;
+}
+
+// per-rank bookkeeping: nnz of each (local row-block, col-block) bucket; comm_seconds = device time of
+// this rank's outgoing copies (copy-engine plane only: each DMA timed behind its hand-shake waits)
 extern "C" int ge_dist_stats(ge_ctx* ctx, int64_t* bucket_nnz, int32_t cap, double* comm_seconds, int64_t* nnz_global) {
     if (!ctx || !ctx->dist) return GE_ERR_STATE;
     DistState* d = ctx->dist;

@@ -76,7 +76,9 @@ class DistTrainer:
         n = self._n.ck(self._n.L.ge_dist_stats(self._n.h, _ptr(b), 1024, C.byref(comm), C.byref(nnzg)))
         s, l, u = C.c_double(0), C.c_int64(0), C.c_int64(0)
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
-        return {"bucket_nnz": b[:n].copy(), "comm_seconds": comm.value, "nnz_global": nnzg.value,
+        rot = {-1: "pointer shift (1 GPU)", 0: "nccl send/recv in-stream", 1: "nccl half blocks, second stream",
+               2: "copy engine into the neighbour's IPC-mapped ring"}.get(self._n.L.ge_dist_rotation_mode(self._n.h), "?")
+        return {"bucket_nnz": b[:n].copy(), "comm_seconds": comm.value, "nnz_global": nnzg.value, "rotation": rot,
                 "update_seconds": s.value, "launches": l.value, "updates": u.value}
 
     def set_stream(self, s):

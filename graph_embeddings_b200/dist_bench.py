@@ -60,8 +60,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
     else:
         nnz_local, _ = tr.build(g)
     tr.prepare()
-    for _ in range(K):
-        tr.epoch()
+    e2e_costs = [tr.epoch() for _ in range(K)]
     # result D2H: every rank pulls its own rows; guarded so that `world` result buffers (C5: 7.5 GB
     # each) never exhaust the host's memory
     import psutil
@@ -104,6 +103,21 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
     else:
         allst = [stats]
     clk = clocks.stop() if clocks else None
+    # ---- correctness of the N-rank data plane: rank 0 walks the SAME schedule alone (world = 1: same
+    # buckets, same per-bucket order keys, rotation = pointer shift) from the same init and compares
+    # the first epochs' loss with what the N ranks produced (only the Hogwild interleaving differs)
+    check = None
+    if world > 1 and not direct and os.environ.get("GE_BENCH_CHECK", "1") != "0":
+        if rank == 0:
+            t1 = DistTrainer(cfg, 0, 1, 8, None)
+            t1.build(g)
+            t1.prepare()
+            ne = min(3, K)
+            h1 = [t1.epoch() for _ in range(ne)]
+            del t1
+            check = {"epochs": ne, "loss_n_ranks": e2e_costs[:ne], "loss_1_rank": h1,
+                     "max_rel_loss_diff_vs_1rank": max(abs(a - b) / b for a, b in zip(e2e_costs[:ne], h1))}
+        barrier()
     if rank == 0:
         A = torch.stack(allst).cpu().numpy()
         ms = float(ms.item())
@@ -117,11 +131,11 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
                 "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
                 "scaling": "weak" if direct else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": desc, "V": V if direct else g.V, "E": 0 if direct else g.E, "nnz": int(nnz), "dim": dim, "alpha": ALPHA, "epsilon": EPS,
-                           "method": "glove", "optimizer": "adagrad", "parallelism": f"8x8 block rotation over {world} GPU(s), "
-                           "NCCL send/recv of one C block per sub-epoch", "math": "f32 fast path, atomic red.add row updates",
+                           "method": "glove", "optimizer": "adagrad", "parallelism": f"8x8 block rotation over {world} GPU(s); rotation: {s1['rotation']}", "math": "f32 fast path, atomic red.add row updates",
                            "l2": "inputs larger than L2", "final_cost": costs[-1],
                            "nnz_per_rank": [int(x) for x in A[:, 5]],
-                           "rotation_seconds_per_epoch_max": float(A[:, 4].max() / K)},
+                           "rotation_copy_seconds_per_epoch_max": float(A[:, 4].max() / K),
+                           "check_vs_1rank": check},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
                              "frac": achieved / (peak * world), "traffic": None, "kernel": "glove_adagrad_update",
                              "bytes_per_nnz": B, "peak_source": peak_src + f" x {world} GPUs",

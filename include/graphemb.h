@@ -263,7 +263,14 @@ int ge_dist_prepare(ge_ctx*, int32_t nblocks);
 int ge_dist_train_epoch(ge_ctx*, double* cost);
 /* (W+C)/2 of this rank's id range, row-major count x dim */
 int ge_dist_extract_f32(ge_ctx*, float* out, int64_t cap);
-/* returns the number of local buckets and fills their nnz; seconds spent in rotations */
+/* data plane of the rotation in use: 2 = half blocks pushed by the copy engine into the neighbour's ring
+ * (CUDA IPC mapping, flag hand-shake with stream memory operations; default), 1 = half-block
+ * ncclSend/ncclRecv on a second stream (GE_DIST_ROT=pipe, or the fallback when IPC is unavailable),
+ * 0 = whole-block ncclSend/ncclRecv in the compute stream (GE_DIST_ROT=nccl), -1 = single GPU */
+int ge_dist_rotation_mode(ge_ctx*);
+/* returns the number of local buckets and fills their nnz; comm_seconds = device time of this rank's
+ * outgoing block copies (copy-engine plane; 0 for the NCCL planes, whose send/recv time includes
+ * waiting for the peer) */
 int ge_dist_stats(ge_ctx*, int64_t* bucket_nnz, int32_t cap, double* comm_seconds, int64_t* nnz_global);
 
 #ifdef __cplusplus

@@ -61,6 +61,8 @@ def lib():
         L.orc_train_get_perm.argtypes = [p, p]
         L.orc_train_optimize.argtypes = [p, i32, f64, p, p]
         L.orc_train_optimize.restype = i32
+        L.orc_train_history_exact.argtypes = [p, p, i32]
+        L.orc_train_history_exact.restype = i32
         L.orc_train_extract.argtypes = [p, p]
         L.orc_train_get_store.argtypes = [p, i32, p]
         L.orc_train_free.argtypes = [p]
@@ -169,6 +171,14 @@ class Trainer:
         fc = C.c_double(0)
         n = lib().orc_train_optimize(self._h, maxiter, tolerance, _ptr(hist), C.byref(fc))
         return hist[:n].copy(), fc.value
+
+    def history_exact(self) -> np.ndarray:
+        """Per-epoch cost of the epochs run so far with the job sums kept in fp64.  NOT what the
+        reference reports: Adagrad.java:60 accumulates in a float, which stops absorbing increments
+        after some 10-30 M nonzeros per thread (see oracle.cpp Trainer::job)."""
+        out = np.zeros(65536, np.float64)
+        n = lib().orc_train_history_exact(self._h, _ptr(out), len(out))
+        return out[:n].copy()
 
     def extract(self) -> np.ndarray:
         out = np.empty((self.V, self.dim), np.float64)
