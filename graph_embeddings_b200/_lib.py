@@ -81,6 +81,7 @@ SIGNATURES = {
     "ge_extract_f32": (C.c_int, [_P, _P]),
     "ge_store_export": (C.c_int, [_P, _I32, _P]),
     "ge_epoch_order": (C.c_int, [_P, _I32, _P, _I64]),
+    "ge_train_reset": (C.c_int, [_P]),
     "ge_train_stats": (C.c_int, [_P, C.POINTER(_F64), C.POINTER(_I64), C.POINTER(_I64)]),
     "ge_write_embeddings": (C.c_int, [_P, C.c_char_p, C.c_char_p, C.c_char_p, _P, _P, _P, _P, _P, C.POINTER(_I64)]),
     "ge_format_e": (C.c_int, [_F64, C.c_char_p, _I32]),

@@ -337,6 +337,12 @@ class Adagrad(IOptimizer):
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
         return {"update_seconds": s.value, "launches": l.value, "updates": u.value}
 
+    def reset(self):
+        """A fresh optimizer on the same matrix (new Adagrad(coMatrix, ...), Main.java:72): store
+        re-initialised, nonzeros re-packed."""
+        self._n.ck(self._n.L.ge_train_reset(self._n.h))
+        self._n.ck(self._n.L.ge_store_init(self._n.h))
+
 
 class Adam(Adagrad):
     """new Adam(coMatrix, config, costFunction) (J/opt/grad/Adam.java:55-66); same epoch loop

@@ -78,6 +78,7 @@ struct __align__(16) NzEntry {
 };
 #define GE_ID_BITS 27
 #define GE_ID_MASK 0x07ffffff
+#define GE_ID_KEEP ((int32_t)0x80000000)  // bit 31: row belongs to the L2-resident set (evict_last cache policy)
 // Damping exponent of an id that occurs `cnt` times where `hot_count` occurrences mean
 // GE_HOT_WRITERS expected concurrent writers: the smallest k >= 1 with cnt * 2^(-k/2) < hot_count
 // (capped at 15), so that the scaled deltas of all concurrent writers add up to between
@@ -131,6 +132,7 @@ struct ge_ctx {
     JavaLcg rng{0};               // stream position after init (GE_ORDER_JAVA)
     double* d_cost = nullptr;     // epoch cost accumulator
     bool any_hot = false;         // packed nonzeros carry hub damping exponents
+    int32_t keep_count = 0x7fffffff;  // ids occurring at least this often are in the L2-resident set
     int32_t epoch = 0;
     std::vector<double> history;
     double update_seconds = 0;
@@ -151,6 +153,8 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
 void ge_free_store(ge_ctx* ctx);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (damped deltas)
+void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i, const int32_t* cnt_j, int64_t nj,
+                    double div_j, double share_j, int32_t* keep_i, int32_t* keep_j);  // L2-resident set thresholds (raw occurrence counts)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
 int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
 // sim.cu

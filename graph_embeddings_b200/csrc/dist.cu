@@ -159,8 +159,8 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
                                const float* __restrict__ X, int64_t nnz, int32_t row_base, int32_t Bs, int32_t nb,
                                int32_t P, int32_t Hs, int32_t method, double xmax, unsigned long long* __restrict__ cursor,
                                const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
-                               const int32_t* __restrict__ hot_cnt, int32_t m, int32_t* __restrict__ any_hot,
-                               NzEntry* __restrict__ out) {
+                               const int32_t* __restrict__ hot_cnt, int32_t m, int32_t keep_i, int32_t keep_j,
+                               int32_t* __restrict__ any_hot, NzEntry* __restrict__ out) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
         const int32_t i = I[k] - row_base, j = J[k];
@@ -176,6 +176,8 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
         const int32_t ki = ge_damp_bits(cnt_i[i] / (nb * P), hot_cnt[b]), kj = ge_damp_bits(cnt_j[j] / m, hot_cnt[b]);
         if (ki) { e.i |= ki << GE_ID_BITS; any_hot[b] = 1; }
         if (kj) { e.j |= kj << GE_ID_BITS; any_hot[b] = 1; }
+        if (cnt_i[i] >= keep_i) e.i |= GE_ID_KEEP;  // L2-resident set (train.cu ge_keep_counts)
+        if (cnt_j[j] >= keep_j) e.j |= GE_ID_KEEP;
         if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
             e.b = ((double)x > xmax) ? 1.0f : (float)pow((double)x / xmax, 0.75);
@@ -420,11 +422,16 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         for (int b = 0; b < nbuckets; b++) if (flags) hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs);
         r = ge_count_ids(ctx, ctx->d_I, ctx->nnz, first, (int64_t)d->m * d->Bs, &cnt_i);
         if (!r) r = ge_count_ids(ctx, ctx->d_J, ctx->nnz, 0, (int64_t)d->nb * d->Bs, &cnt_j);
+        int32_t keep_i = 0x7fffffff, keep_j = 0x7fffffff;
+        // one launch = one (row-block, half column-block) bucket: it sees 1/(nb*P) of a row's and 1/m of a
+        // column's local nonzeros; 1/m of the rank's flagged W rows and 1/(nb*P) of the flagged C rows are live
+        if (!r) ge_keep_counts(ctx, cnt_i, (int64_t)d->m * d->Bs, (double)d->nb * d->P, 1.0 / d->m,
+                               cnt_j, (int64_t)d->nb * d->Bs, (double)d->m, 1.0 / ((double)d->nb * d->P), &keep_i, &keep_j);
         cudaError_t e = r ? cudaSuccess : cudaMalloc(&d_hot, 2048 * 4);
         if (!r && e == cudaSuccess) e = cudaMemcpyAsync(d_hot, hot.data(), 2048 * 4, cudaMemcpyHostToDevice, st);
         if (!r && e == cudaSuccess && ctx->nnz > 0)
             bucket_scatter<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, first, d->Bs, d->nb,
-                                                             d->P, d->Hs, c.method, ctx->xmax, d_cnt, cnt_i, cnt_j, d_hot, d->m, d_hot + 1024, d->d_nzb);
+                                                             d->P, d->Hs, c.method, ctx->xmax, d_cnt, cnt_i, cnt_j, d_hot, d->m, keep_i, keep_j, d_hot + 1024, d->d_nzb);
         if (!r && e == cudaSuccess) e = cudaGetLastError();
         if (!r && e == cudaSuccess) e = cudaMemcpyAsync(hot.data() + 1024, d_hot + 1024, 1024 * 4, cudaMemcpyDeviceToHost, st);
         if (!r && e == cudaSuccess) e = cudaStreamSynchronize(st);

@@ -32,6 +32,39 @@ __device__ __forceinline__ float2 ldcg2v(const float* p) {
 }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
+// L2 residency control.  The store is far larger than the 126 MB L2 and rows are visited in a uniformly
+// shuffled order, so under plain LRU a row survives between two of its visits only if it is touched
+// every ~50 us (C4: degree > ~19 000): the read hit rate is 13 % (profiles/r02_update_c4_ncu.md).
+// Rows whose occurrence count puts them among the ~60 000 most visited (bit 31 of the packed id, set
+// at pack time) are loaded and reduced with an evict_last cache policy, everything else with
+// evict_normal: the hot set then stays resident for the whole epoch.
+__device__ __forceinline__ uint64_t l2_policy_keep() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_stream() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ float4 ldcg4p(const float* p, uint64_t pol) {
+    float4 v;
+    asm volatile("ld.global.cg.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 ldcg2p(const float* p, uint64_t pol) {
+    float2 v;
+    asm volatile("ld.global.cg.L2::cache_hint.v2.f32 {%0, %1}, [%2], %3;" : "=f"(v.x), "=f"(v.y) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red4p(float* p, float a, float b, float c, float d, uint64_t pol) {
+    asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void red2p(float* p, float a, float b, uint64_t pol) {
+    asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.v2.f32 [%0], {%1, %2}, %3;" ::"l"(p), "f"(a), "f"(b), "l"(pol) : "memory");
+}
+
 // vector float reduction at L2 (sm_90+): no value returns to the SM, updates are never lost
 __device__ __forceinline__ void red4(float* p, float a, float b, float c, float d) {
     asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -130,6 +163,7 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
     const double lr_d = (double)lr;
     double cost_d = 0.0;
     float cost_f = 0.0f;  // JAVA: the reference's f32 running cost (Adagrad.java:46,60)
+    const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
 
     auto fetch = [&](int64_t pos) -> NzEntry {  // lane l fetches the nonzero at shuffled position pos
         NzEntry e = {0, 0, 0.f, 0.f};
@@ -199,6 +233,8 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                 si = exp2f(-0.5f * (float)((bi >> GE_ID_BITS) & 15));
                 sj = exp2f(-0.5f * (float)((bj >> GE_ID_BITS) & 15));
             }
+            // bit 31 = row is in the L2-resident set (pack time): warp-uniform choice of the cache policy
+            const uint64_t polw = bi < 0 ? pol_keep : pol_stream, polc = bj < 0 ? pol_keep : pol_stream;
             bi &= GE_ID_MASK; bj &= GE_ID_MASK;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
@@ -231,26 +267,26 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                 // measured on B200 (C3 graph): d=128 134.4 vs 141.8 ms, d=300 325 vs 370 ms per
                 // epoch; for rows narrower than a warp (d=100: 119.8 vs 107.7 ms) everything up
                 // front is faster, so the launcher picks by D4 (profiles/r01_load_order.md).
-                auto ldv = [&](float4 (&a)[NT], const float* base, float fill) {
+                auto ldv = [&](float4 (&a)[NT], const float* base, float fill, uint64_t pol) {
 #pragma unroll
                     for (int q = 0; q < NT; q++) {
                         const int ch = lane + 32 * q;
-                        a[q] = ch < nchunk ? ldcg4v(base + 4 * ch) : make_float4(fill, fill, fill, fill);
+                        a[q] = ch < nchunk ? ldcg4p(base + 4 * ch, pol) : make_float4(fill, fill, fill, fill);
                     }
                 };
-                ldv(w, wrow, 0.f);
-                ldv(c, crow, 0.f);
+                ldv(w, wrow, 0.f, polw);
+                ldv(c, crow, 0.f, polc);
                 if (!two_phase) {
-                    ldv(gw, wrow + D4, 1.f); ldv(gc, crow + D4, 1.f);
-                    bw = ldcg2v(wrow + 2 * D4); bc = ldcg2v(crow + 2 * D4);
+                    ldv(gw, wrow + D4, 1.f, polw); ldv(gc, crow + D4, 1.f, polc);
+                    bw = ldcg2p(wrow + 2 * D4, polw); bc = ldcg2p(crow + 2 * D4, polc);
                 }
 #pragma unroll
                 for (int q = 0; q < NT; q++)
                     dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
                 dot = warp_sum(dot);
                 if (two_phase) {
-                    ldv(gw, wrow + D4, 1.f); ldv(gc, crow + D4, 1.f);
-                    bw = ldcg2v(wrow + 2 * D4); bc = ldcg2v(crow + 2 * D4);
+                    ldv(gw, wrow + D4, 1.f, polw); ldv(gc, crow + D4, 1.f, polc);
+                    bw = ldcg2p(wrow + 2 * D4, polw); bc = ldcg2p(crow + 2 * D4, polc);
                 }
             }
 
@@ -310,10 +346,10 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         }
                     }
                     if (ATOMIC) {
-                        red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
-                        red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
-                        red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
-                        red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
+                        red4p(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w, polw);
+                        red4p(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w, polw);
+                        red4p(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w, polc);
+                        red4p(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w, polc);
                     } else {
                         st4(wrow + 4 * ch, w[q]);
                         st4(crow + 4 * ch, c[q]);
@@ -330,8 +366,8 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
                 } else if (ATOMIC) {
-                    red2(wrow + 2 * D4, -wc * rsqrtf(bw.y) * si, wc * wc);
-                    red2(crow + 2 * D4, -wc * rsqrtf(bc.y) * sj, wc * wc);
+                    red2p(wrow + 2 * D4, -wc * rsqrtf(bw.y) * si, wc * wc, polw);
+                    red2p(crow + 2 * D4, -wc * rsqrtf(bc.y) * sj, wc * wc, polc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
@@ -527,14 +563,22 @@ adam_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W
 __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __restrict__ J,
                               const float* __restrict__ X, int64_t nnz, int32_t method, int32_t java,
                               double xmax, const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
-                              int32_t hot_count, int32_t* __restrict__ any_hot, NzEntry* __restrict__ out) {
+                              int32_t hot_count, int32_t keep_i, int32_t keep_j, int32_t* __restrict__ any_hot, NzEntry* __restrict__ out) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
         const float x = X[k];
         NzEntry e;
         e.i = I[k]; e.j = J[k];
-        if (cnt_i) { const int32_t k = ge_damp_bits(cnt_i[e.i], hot_count); if (k) { e.i |= k << GE_ID_BITS; *any_hot = 1; } }  // hub row
-        if (cnt_j) { const int32_t k = ge_damp_bits(cnt_j[e.j], hot_count); if (k) { e.j |= k << GE_ID_BITS; *any_hot = 1; } }  // hub column
+        if (cnt_i) {  // hub row: damping exponent; L2-resident set: bit 31
+            const int32_t c = cnt_i[e.i], k = ge_damp_bits(c, hot_count);
+            if (k) { e.i |= k << GE_ID_BITS; *any_hot = 1; }
+            if (c >= keep_i) e.i |= GE_ID_KEEP;
+        }
+        if (cnt_j) {  // hub column
+            const int32_t c = cnt_j[e.j], k = ge_damp_bits(c, hot_count);
+            if (k) { e.j |= k << GE_ID_BITS; *any_hot = 1; }
+            if (c >= keep_j) e.j |= GE_ID_KEEP;
+        }
         if (java) { e.a = x; e.b = 0.f; }
         else if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
@@ -795,6 +839,60 @@ __global__ void count_ids(const int32_t* __restrict__ ids, int64_t n, int32_t ba
 }
 }  // namespace
 
+namespace {
+// rows per occurrence-count class (8 classes per octave): input of the L2-resident-set threshold
+__global__ void count_classes(const int32_t* __restrict__ cnt, int64_t n, unsigned long long* __restrict__ hist) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const int32_t c = cnt[k];
+        if (c > 0) atomicAdd(&hist[min(255, (int)(8.0f * log2f((float)c)))], 1ULL);
+    }
+}
+}  // namespace
+
+// Occurrence counts from which a row of W (keep_i) / of C (keep_j) joins the L2-resident set: rows
+// that occur at least that often are loaded / reduced with an evict_last policy (bit 31 of the packed
+// id).  One launch sees about cnt / div of an id's occurrences and `share` of the flagged rows of
+// that side (single GPU: div = share = 1; block trainer: a row's nonzeros spread over the column
+// blocks, and only one row-block / column-block pair is live per launch).  The threshold is on the
+// per-launch count, the same for both sides, as low as the budget GE_L2_KEEP_MB (default 64; 0 = off)
+// allows.  0x7fffffff = nothing qualifies.
+void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i,
+                    const int32_t* cnt_j, int64_t nj, double div_j, double share_j, int32_t* keep_i, int32_t* keep_j) {
+    const double mb = getenv("GE_L2_KEEP_MB") ? atof(getenv("GE_L2_KEEP_MB")) : 64.0;  // read per pack: sweeps change it
+    *keep_i = *keep_j = 0x7fffffff;
+    if (mb <= 0 || !cnt_i || !cnt_j) return;
+    const double budget_rows = mb * 1048576.0 / ((double)ctx->S * 4.0);
+    unsigned long long* d_h = nullptr;
+    unsigned long long h[512];
+    if (cudaMalloc(&d_h, sizeof(h)) != cudaSuccess) { cudaGetLastError(); return; }
+    cudaMemsetAsync(d_h, 0, sizeof(h), ctx->stream);
+    count_classes<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_i, ni, d_h);
+    count_classes<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, nj, d_h + 256);
+    cudaError_t e = cudaMemcpyAsync(h, d_h, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_h);
+    if (e != cudaSuccess) { cudaGetLastError(); return; }
+    // rows of a side whose raw count is at least `raw` (classes are 1/8 octave wide: round the class up)
+    auto at_least = [&](const unsigned long long* hh, double raw) -> double {
+        int cls = raw <= 1.0 ? 0 : (int)ceil(8.0 * log2(raw));
+        double rows = 0;
+        for (int c = cls < 0 ? 0 : cls; c < 256; c++) rows += (double)hh[c];
+        return rows;
+    };
+    double best = -1;
+    for (int t = 8 * 31; t >= 0; t--) {  // per-launch count threshold 2^(t/8), descending
+        const double tau = exp2((double)t / 8.0);
+        const double rows = share_i * at_least(h, tau * div_i) + share_j * at_least(h + 256, tau * div_j);
+        if (rows > budget_rows) break;
+        best = tau;
+    }
+    if (best < 0) return;
+    const double ki = ceil(exp2(ceil(8.0 * log2(fmax(1.0, best * div_i))) / 8.0)), kj = ceil(exp2(ceil(8.0 * log2(fmax(1.0, best * div_j))) / 8.0));
+    *keep_i = ki > 2e9 ? 0x7fffffff : (int32_t)ki;
+    *keep_j = kj > 2e9 ? 0x7fffffff : (int32_t)kj;
+}
+
 // occurrences of every id in [base, base+n) among ids[0..nnz): input of the hot-id flags
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt) {
     *d_cnt = nullptr;
@@ -814,7 +912,7 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 // deltas so the sum stays below GE_HOT_WRITERS full steps.  Returns the occurrence count from which
 // an id is hot.
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
-    static const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
+    const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
     if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
     if (warps < 1) warps = 1;
@@ -838,9 +936,12 @@ int ge_train_prepare(ge_ctx* ctx) {
             if (!r) r = ge_count_ids(ctx, ctx->d_J, ctx->nnz, 0, ctx->V, &cnt_j);
             if (r) { cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_any); return r; }
         }
+        int32_t keep_i, keep_j;
+        ge_keep_counts(ctx, cnt_i, ctx->V, 1.0, 1.0, cnt_j, ctx->V, 1.0, 1.0, &keep_i, &keep_j);
+        ctx->keep_count = keep_i;
         pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
                                                                  c.math == GE_MATH_JAVA, ctx->xmax, cnt_i, cnt_j,
-                                                                 ge_hot_count(ctx, ctx->nnz, ctx->V), d_any, ctx->d_nz);
+                                                                 ge_hot_count(ctx, ctx->nnz, ctx->V), keep_i, keep_j, d_any, ctx->d_nz);
         cudaError_t pe = cudaGetLastError();
         int32_t any = 0;
         if (pe == cudaSuccess) pe = cudaMemcpyAsync(&any, d_any, 4, cudaMemcpyDeviceToHost, ctx->stream);
@@ -1032,6 +1133,17 @@ extern "C" int ge_epoch_order(ge_ctx* ctx, int32_t epoch, int32_t* perm, int64_t
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(d);
     GE_CUDA(e);
+    return GE_OK;
+}
+
+// forget the packed nonzeros and the embedding store: the next epoch re-packs the matrix (re-reading the
+// tuning environment: GE_L2_KEEP_MB, GE_HOT_WRITERS) and starts from a fresh initialisation
+extern "C" int ge_train_reset(ge_ctx* ctx) {
+    if (!ctx) return GE_ERR_INVALID;
+    cudaSetDevice(ctx->cfg.device);
+    ge_free_store(ctx);
+    ctx->epoch = 0;
+    ctx->history.clear();
     return GE_OK;
 }
 

@@ -224,6 +224,9 @@ int ge_extract_f32(ge_ctx*, float* out);
 int ge_store_export(ge_ctx*, int32_t which, float* out);
 /* epoch order used by the last/next epoch as an explicit permutation (validation) */
 int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);
+/* forget the packed nonzeros and the embedding store (the matrix stays): the next epoch re-packs and
+ * starts from a fresh initialisation — a new Optimizer on the same CoOccurrenceMatrix (Main.java:72) */
+int ge_train_reset(ge_ctx*);
 /* device seconds and kernel launches spent in update kernels so far */
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
 

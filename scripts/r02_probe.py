@@ -77,7 +77,8 @@ def zipf():
     out = {"top_col_share": float(np.bincount(J, minlength=V).max() / nnz), "hot_writers": os.environ.get("GE_HOT_WRITERS", "16")}
     t0 = time.time()
     t = oracle.Trainer(V, I, J, X, 0.2, dim, "glove", 31)
-    out["oracle"] = [t.epoch() for _ in range(epochs)]
+    out["oracle_f32sum"] = [t.epoch() for _ in range(epochs)]
+    out["oracle"] = t.history_exact().tolist()          # fp64-summed loss of the same trajectory
     out["oracle_s"] = time.time() - t0
     t.close()
     for upd in ("atomic", "store"):
@@ -128,5 +129,30 @@ def blocks():
         json.dump(out, f)
 
 
+def keep():
+    """C4 (or PROBE_WL) on one GPU: L2-resident hot-row budget sweep, same matrix, fresh init each time"""
+    import torch
+    from graph_embeddings_b200 import BCA, BookmarkColoring, Configuration, Opt, createOptimizer, synth
+    wl = os.environ.get("PROBE_WL", "c4")
+    V, E = {"c4": (10_000_000, 100_000_000), "c3": (2_000_000, 20_000_000)}[wl]
+    dim = int(os.environ.get("PROBE_DIM", "128"))
+    g = synth.rmat_torch(V, E, 5, device="cuda")
+    epochs = 4
+    c = Configuration(method="glove", dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=12345)
+    bca = BookmarkColoring(g, c)
+    opt = createOptimizer(c, bca)
+    out = {"workload": wl, "dim": dim, "nnz": bca.coOccurrenceCount()}
+    for mb in os.environ.get("PROBE_KEEP", "0,32,64,96").split(","):
+        os.environ["GE_L2_KEEP_MB"] = mb
+        opt.reset()
+        s0 = opt.stats()["update_seconds"]
+        hist = [opt.epoch() for _ in range(epochs)]
+        ms = (opt.stats()["update_seconds"] - s0) / epochs * 1e3
+        out[f"keep{mb}"] = {"ms": ms, "hist": hist}
+        print(f"keep {mb} MB: {ms:.1f} ms/epoch hist {np.round(hist, 6)}", flush=True)
+    with open(os.path.join(OUT, f"probe_keep_{wl}_d{dim}.json"), "w") as f:
+        json.dump(out, f)
+
+
 if __name__ == "__main__":
-    {"parity": lambda: parity(sys.argv[2:]), "zipf": zipf, "blocks": blocks}[sys.argv[1]]()
+    {"parity": lambda: parity(sys.argv[2:]), "zipf": zipf, "blocks": blocks, "keep": keep}[sys.argv[1]]()
