@@ -4,6 +4,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <thread>
+
 static std::string g_create_err;
 
 namespace {
@@ -53,22 +55,62 @@ __global__ void check_ids(const int32_t* __restrict__ I, const int32_t* __restri
     if (b) *bad = 1;
 }
 
-int check_csr(ge_ctx* ctx, int32_t V, const int64_t* off, const int32_t* nbr, const char* name) {
-    if (off[0] != 0) { ctx->err = std::string(name) + "_off[0] != 0"; return GE_ERR_GRAPH; }
-    for (int32_t v = 0; v < V; v++) {
-        if (off[v + 1] < off[v]) { ctx->err = std::string(name) + "_off not monotone"; return GE_ERR_GRAPH; }
+// CSR validation on the device (one pass over the arrays already uploaded): offsets start at 0 and
+// never decrease, every neighbour id is in range, every list is sorted by id and unique — the form
+// getIn/OutNeighborhoods hands over (BookmarkColoring.java:49-50).  code: 1 off[0], 2 monotone,
+// 3 id range, 4 order.
+__global__ void check_csr_dev(const int64_t* __restrict__ off, const int32_t* __restrict__ nbr, int32_t V, int64_t E,
+                              int32_t* __restrict__ code) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t0 == 0 && (off[0] != 0 || off[V] != E)) atomicMax(code, 1);
+    for (int64_t v = t0; v < V; v += stride) {
+        const int64_t b = off[v], e = off[v + 1];
+        if (e < b || b < 0 || e > E) { atomicMax(code, 2); continue; }
         int64_t prev = -1;
-        for (int64_t k = off[v]; k < off[v + 1]; k++) {
+        for (int64_t k = b; k < e; k++) {
             const int64_t u = nbr[k];
-            if (u < 0 || u >= V) { ctx->err = std::string(name) + "_nbr id out of range"; return GE_ERR_GRAPH; }
-            if (u <= prev) { ctx->err = std::string(name) + " neighbour lists must be sorted by id and unique"; return GE_ERR_GRAPH; }
+            if (u < 0 || u >= V) { atomicMax(code, 3); break; }
+            if (u <= prev) { atomicMax(code, 4); break; }
             prev = u;
         }
     }
-    return GE_OK;
 }
 
 }  // namespace
+
+// Host -> device copy of a pageable buffer through two pinned staging buffers: host threads fill one
+// while the other crosses PCIe (the driver's own pageable path stages single-threaded, 3-6 GB/s).
+int upload_staged(ge_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    if (!bytes) return GE_OK;
+    cudaStream_t st = ctx->stream;
+    if (bytes < ((size_t)8 << 20)) { GE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st)); return GE_OK; }
+    const size_t chunk = (size_t)32 << 20;
+    if (!ctx->h_stage[0]) {
+        for (int k = 0; k < 2; k++) {
+            GE_CUDA(cudaMallocHost(&ctx->h_stage[k], chunk));
+            GE_CUDA(cudaEventCreateWithFlags(&ctx->ev_stage[k], cudaEventDisableTiming));
+        }
+    }
+    unsigned nthr = std::thread::hardware_concurrency();
+    nthr = nthr < 1 ? 1 : (nthr > 8 ? 8 : nthr);
+    const size_t n = (bytes + chunk - 1) / chunk;
+    for (size_t c = 0; c < n; c++) {
+        const int b = (int)(c & 1);
+        const size_t o = c * chunk, len = bytes - o < chunk ? bytes - o : chunk;
+        if (c >= 2) GE_CUDA(cudaEventSynchronize(ctx->ev_stage[b]));  // the copy out of this buffer two chunks ago is done
+        char* h = (char*)ctx->h_stage[b];
+        const char* sp = (const char*)src + o;
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nthr; t++) {
+            const size_t lo = len * t / nthr, hi = len * (t + 1) / nthr;
+            th.emplace_back([=] { memcpy(h + lo, sp + lo, hi - lo); });
+        }
+        for (auto& x : th) x.join();
+        GE_CUDA(cudaMemcpyAsync((char*)dst + o, h, len, cudaMemcpyHostToDevice, st));
+        GE_CUDA(cudaEventRecord(ctx->ev_stage[b], st));
+    }
+    return GE_OK;
+}
 
 void ge_free_graph(ge_ctx* ctx) {
     cudaFree(ctx->d_out_off); cudaFree(ctx->d_in_off); cudaFree(ctx->d_out_nbr); cudaFree(ctx->d_in_nbr);
@@ -181,8 +223,55 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     ge_free_graph(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (int k = 0; k < 2; k++) {
+        if (ctx->h_stage[k]) cudaFreeHost(ctx->h_stage[k]);
+        if (ctx->ev_stage[k]) cudaEventDestroy(ctx->ev_stage[k]);
+    }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
+}
+
+// device-side checks of the CSR now resident + per-node totals (both hand-off paths end here)
+int ge_graph_validate(ge_ctx* ctx) {
+    int32_t* d_code = nullptr;
+    int32_t code[2] = {0, 0};
+    GE_CUDA(cudaMalloc(&d_code, 8));
+    cudaError_t e = cudaMemsetAsync(d_code, 0, 8, ctx->stream);
+    if (e == cudaSuccess) {
+        check_csr_dev<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_out_off, ctx->d_out_nbr, ctx->V, ctx->E_out, d_code);
+        check_csr_dev<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_in_off, ctx->d_in_nbr, ctx->V, ctx->E_in, d_code + 1);
+        e = cudaMemcpyAsync(code, d_code, 8, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_code);
+    GE_CUDA(e);
+    for (int k = 0; k < 2; k++) {
+        if (!code[k]) continue;
+        const char* name = k ? "in" : "out";
+        const char* what[] = {"", "_off[0] != 0 or _off[V] != E", "_off not monotone", "_nbr id out of range",
+                              " neighbour lists must be sorted by id and unique"};
+        ctx->err = std::string(name) + what[code[k]];
+        ge_free_graph(ctx);
+        return GE_ERR_GRAPH;
+    }
+    return GE_OK;
+}
+
+int ge_graph_alloc(ge_ctx* ctx, int32_t V, int64_t E_out, int64_t E_in) {
+    ge_free_graph(ctx);
+    ge_free_cooc(ctx);
+    ge_free_store(ctx);
+    ctx->V = V;
+    ctx->E_out = E_out;
+    ctx->E_in = E_in;
+    const size_t ob = (size_t)(V + 1) * sizeof(int64_t);
+    GE_CUDA(cudaMalloc(&ctx->d_out_off, ob));
+    GE_CUDA(cudaMalloc(&ctx->d_in_off, ob));
+    GE_CUDA(cudaMalloc(&ctx->d_out_nbr, (size_t)(E_out + 1) * 4));
+    GE_CUDA(cudaMalloc(&ctx->d_out_w, (size_t)(E_out + 1) * 4));
+    GE_CUDA(cudaMalloc(&ctx->d_in_nbr, (size_t)(E_in + 1) * 4));
+    GE_CUDA(cudaMalloc(&ctx->d_in_w, (size_t)(E_in + 1) * 4));
+    return GE_OK;
 }
 
 extern "C" int ge_set_graph_csr(ge_ctx* ctx, int32_t V, const int64_t* out_off, const int32_t* out_nbr,
@@ -190,37 +279,24 @@ extern "C" int ge_set_graph_csr(ge_ctx* ctx, int32_t V, const int64_t* out_off, 
                                 const float* in_w) {
     if (!ctx) return GE_ERR_INVALID;
     if (V <= 0 || !out_off || !in_off) { ctx->err = "bad graph arguments"; return GE_ERR_INVALID; }
+    if (out_off[V] < 0 || in_off[V] < 0 || (out_off[V] > 0 && (!out_nbr || !out_w)) || (in_off[V] > 0 && (!in_nbr || !in_w))) {
+        ctx->err = "bad graph arguments"; return GE_ERR_INVALID;
+    }
     cudaSetDevice(ctx->cfg.device);
-    int r = check_csr(ctx, V, out_off, out_nbr, "out");
-    if (r) return r;
-    r = check_csr(ctx, V, in_off, in_nbr, "in");
-    if (r) return r;
-    ge_free_graph(ctx);
-    ge_free_cooc(ctx);
-    ge_free_store(ctx);
-    ctx->V = V;
-    ctx->E_out = out_off[V];
-    ctx->E_in = in_off[V];
+    int r = ge_graph_alloc(ctx, V, out_off[V], in_off[V]);
+    if (r) { ge_free_graph(ctx); return r; }
     const size_t ob = (size_t)(V + 1) * sizeof(int64_t);
-    GE_CUDA(cudaMalloc(&ctx->d_out_off, ob));
-    GE_CUDA(cudaMalloc(&ctx->d_in_off, ob));
-    GE_CUDA(cudaMalloc(&ctx->d_out_nbr, (size_t)(ctx->E_out + 1) * 4));
-    GE_CUDA(cudaMalloc(&ctx->d_out_w, (size_t)(ctx->E_out + 1) * 4));
-    GE_CUDA(cudaMalloc(&ctx->d_in_nbr, (size_t)(ctx->E_in + 1) * 4));
-    GE_CUDA(cudaMalloc(&ctx->d_in_w, (size_t)(ctx->E_in + 1) * 4));
-    cudaStream_t s = ctx->stream;
-    GE_CUDA(cudaMemcpyAsync(ctx->d_out_off, out_off, ob, cudaMemcpyHostToDevice, s));
-    GE_CUDA(cudaMemcpyAsync(ctx->d_in_off, in_off, ob, cudaMemcpyHostToDevice, s));
-    if (ctx->E_out) {
-        GE_CUDA(cudaMemcpyAsync(ctx->d_out_nbr, out_nbr, (size_t)ctx->E_out * 4, cudaMemcpyHostToDevice, s));
-        GE_CUDA(cudaMemcpyAsync(ctx->d_out_w, out_w, (size_t)ctx->E_out * 4, cudaMemcpyHostToDevice, s));
+    const struct { void* d; const void* h; size_t n; } parts[] = {
+        {ctx->d_out_off, out_off, ob}, {ctx->d_in_off, in_off, ob},
+        {ctx->d_out_nbr, out_nbr, (size_t)ctx->E_out * 4}, {ctx->d_out_w, out_w, (size_t)ctx->E_out * 4},
+        {ctx->d_in_nbr, in_nbr, (size_t)ctx->E_in * 4}, {ctx->d_in_w, in_w, (size_t)ctx->E_in * 4}};
+    for (const auto& q : parts) {
+        r = upload_staged(ctx, q.d, q.h, q.n);
+        if (r) { ge_free_graph(ctx); return r; }
     }
-    if (ctx->E_in) {
-        GE_CUDA(cudaMemcpyAsync(ctx->d_in_nbr, in_nbr, (size_t)ctx->E_in * 4, cudaMemcpyHostToDevice, s));
-        GE_CUDA(cudaMemcpyAsync(ctx->d_in_w, in_w, (size_t)ctx->E_in * 4, cudaMemcpyHostToDevice, s));
-    }
-    GE_CUDA(cudaStreamSynchronize(s));
     ctx->graph_seconds = 0;
+    r = ge_graph_validate(ctx);   // synchronises: the caller's buffers are free again
+    if (r) return r;
     return ge_graph_finish(ctx);
 }
 

@@ -8,8 +8,9 @@
 //
 // One warp owns one bookmark.  The TreeMap frontier and the BCV HashMap of the reference become
 // ONE per-warp record table {node id | active bit, wet paint (fp64), f32 sum fwd, f32 sum rev}
-// with an open-addressing index.  pollFirstEntry() = warp-wide min over the active keys
-// (REDUX.MIN).  Because a bookmark's events are all produced by its own warp, in pop order, the
+// with an open-addressing index and a compact list of the records currently in the frontier.
+// pollFirstEntry() = warp-wide min over the keys of that list (REDUX.MIN): O(frontier / 32) per
+// pop, however many records the bookmark has retired.  Because a bookmark's events are all produced by its own warp, in pop order, the
 // float32 "add in pop order" of BCV.add needs no global sort: results are bit-exact by
 // construction (fp64 paint with explicit round-to-nearest ops, no FMA contraction).
 // Table tier 1 lives in shared memory (cap 512 records); bookmarks that outgrow it are re-run
@@ -22,7 +23,7 @@
 namespace {
 
 constexpr uint32_t INACTIVE = 0x80000000u;
-constexpr int T1_CAP = 512;          // tier-1 records per warp (shared memory)
+constexpr int T1_CAP = 472;          // tier-1 records per warp (shared memory): 25 B each + 2 KB index -> 8 blocks of 2 warps per SM
 constexpr int T1_WARPS = 2;          // warps per block in tier 1
 constexpr int MAX_ARENAS = 8;
 
@@ -76,6 +77,7 @@ struct Table {
     uint8_t* flg;    // bit0: popped in fwd, bit1: popped in rev
     HT* hash;        // record index + 1, 0 = empty
     HT* ord;         // record indices in first-pop order (= the order BCV entries are created)
+    HT* act;         // record indices of the frontier (TreeMap contents), unordered
     int32_t cap;
     uint32_t hshift, hmask;
 
@@ -106,24 +108,31 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
                         unsigned long long& pops, unsigned long long& scanned) {
     const unsigned FULL = 0xffffffffu;
     const uint8_t bit = (uint8_t)(1 << pass);
-    for (;;) {
-        // pollFirstEntry(): smallest active node id (DirectedWeighted.java:48)
+    const unsigned lt = (1u << lane) - 1;
+    // the frontier holds the bookmark alone (record 0) when a pass starts (:39)
+    if (lane == 0) T.act[0] = 0;
+    int nact = 1;
+    __syncwarp();
+    while (nact > 0) {
+        // pollFirstEntry(): smallest node id in the frontier (DirectedWeighted.java:48)
         uint32_t best = 0xffffffffu;
-        int bidx = -1;
-        for (int c = lane; c < n; c += 32) {
-            const uint32_t k = T.key[c];
-            if (k < best) { best = k; bidx = c; }
+        int bpos = -1;
+        for (int c = lane; c < nact; c += 32) {
+            const uint32_t k = T.key[T.act[c]];
+            if (k < best) { best = k; bpos = c; }
         }
         const uint32_t m = __reduce_min_sync(FULL, best);
-        if (m & INACTIVE) break;  // frontier empty
         const unsigned who = __ballot_sync(FULL, best == m);
-        const int idx = __shfl_sync(FULL, bidx, __ffs(who) - 1);
+        const int pos = __shfl_sync(FULL, bpos, __ffs(who) - 1);
+        const int idx = (int)T.act[pos];
         const int32_t focus = (int32_t)m;
         const double paint = T.wet[idx];
         const bool first_pop = T.flg[idx] == 0;
+        const HT last = T.act[nact - 1];
         __syncwarp();
         if (lane == 0) {
             if (first_pop) T.ord[npop] = (HT)idx;
+            T.act[pos] = last;  // remove from the frontier
             T.wet[idx] = 0.0;
             T.key[idx] = m | INACTIVE;
             // bcv.add(focusNode, alpha * wetPaint) (:53) -> BCV.add(int,float) :35-37
@@ -133,6 +142,7 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
             acc[idx] = (f & bit) ? __fadd_rn(acc[idx], v) : __fadd_rn(0.0f, v);
             T.flg[idx] = f | bit;
         }
+        nact--;
         pops++;
         npop += first_pop ? 1 : 0;
         __syncwarp();
@@ -164,9 +174,11 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
                     take = !(partial < P.eps);  // :85
                 }
                 int rec = -1;
+                bool wake = false;  // known node that is not in the frontier: put() after an earlier pop (:92-96)
                 if (take) {
                     rec = T.find(nb);
-                    if (rec >= 0) {  // :89-91 addPaint, or :92-96 put after an earlier pop
+                    if (rec >= 0) {  // :89-91 addPaint, or :92-96
+                        wake = (T.key[rec] & INACTIVE) != 0;
                         T.wet[rec] = __dadd_rn(T.wet[rec], partial);
                         T.key[rec] = nb;
                     }
@@ -176,16 +188,21 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
                 if (cnt) {
                     if (n + cnt > T.cap) return -1;
                     if (take && rec < 0) {
-                        const int r = n + __popc(newmask & ((1u << lane) - 1));
-                        T.key[r] = nb;
-                        T.wet[r] = partial;
-                        T.accf[r] = 0.f;
-                        T.accr[r] = 0.f;
-                        T.flg[r] = 0;
-                        T.insert(nb, r);
+                        rec = n + __popc(newmask & lt);
+                        T.key[rec] = nb;
+                        T.wet[rec] = partial;
+                        T.accf[rec] = 0.f;
+                        T.accr[rec] = 0.f;
+                        T.flg[rec] = 0;
+                        T.insert(nb, rec);
+                        wake = true;
                     }
                     n += cnt;
                 }
+                // neighbour lists are sorted and unique: no two lanes of a batch see the same record
+                const unsigned wakemask = __ballot_sync(FULL, wake);
+                if (wake) T.act[nact + __popc(wakemask & lt)] = (HT)rec;
+                nact += __popc(wakemask);
                 __syncwarp();
             }
         }
@@ -203,7 +220,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
     {
         uint8_t* p;
         if (SMEM) {
-            const size_t per = (size_t)P.cap * (8 + 4 + 4 + 4 + 1 + sizeof(HT)) + (size_t)hcap * sizeof(HT);
+            const size_t per = (size_t)P.cap * (8 + 4 + 4 + 4 + 1 + 2 * sizeof(HT)) + (size_t)hcap * sizeof(HT);
             p = smem + (size_t)wib * ((per + 15) & ~(size_t)15);
         } else {
             const size_t gw = (size_t)blockIdx.x * (blockDim.x >> 5) + wib;
@@ -216,6 +233,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         T.accr = reinterpret_cast<float*>(p); p += (size_t)P.cap * 4;
         T.hash = reinterpret_cast<HT*>(p); p += (size_t)hcap * sizeof(HT);
         T.ord = reinterpret_cast<HT*>(p); p += (size_t)P.cap * sizeof(HT);
+        T.act = reinterpret_cast<HT*>(p); p += (size_t)P.cap * sizeof(HT);
         T.flg = p;
         T.cap = P.cap; T.hshift = 32 - P.hcap_log2; T.hmask = hcap - 1;
     }
@@ -442,7 +460,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
 
     // tier-1 launch geometry
     const int hcap1_log2 = 10;  // 1024 slots for 512 records
-    const size_t per1 = (((size_t)T1_CAP * 23 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
+    const size_t per1 = (((size_t)T1_CAP * 25 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
     const size_t smem1 = per1 * T1_WARPS;
     GE_CUDA(cudaFuncSetAttribute(bca_push<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     int bps1 = 1;
@@ -496,7 +514,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
             overflow_rows += n_over;
             int hl = 1;
             while (((int64_t)1 << hl) < 2 * cap2) hl++;
-            const size_t per2 = (((size_t)cap2 * 25 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
+            const size_t per2 = (((size_t)cap2 * 29 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
             int64_t warps = (int64_t)ctx->sm_count * 16;
             if (warps > n_over) warps = n_over;
             size_t fb = 0, tb = 0;

@@ -67,9 +67,10 @@ struct JavaLcg {
 };
 
 // One co-occurrence nonzero as the update kernel reads it (16 B, one LDG.128).  Bits 27..30 of i / j
-// carry the damping exponent k of a hub row / column (ge_damp_bits): the FAST/ATOMIC kernel scales
-// that side's delta by 2^(-k/2).  Ids therefore stay below 2^27 (GE_ID_MASK) — no restriction next
-// to the reference, whose int-indexed focus[] needs V * dim < 2^31.
+// carry the concurrency class k of a hub row / column (ge_damp_bits): the FAST/ATOMIC kernel corrects
+// that side's delta for the ~K = GE_HOT_WRITERS * 2^((k-0.5)/2) warps that read the same stale row
+// (train.cu).  Bit 31 marks the rows kept resident in L2.  Ids therefore stay below 2^27 (GE_ID_MASK)
+// — no restriction next to the reference, whose int-indexed focus[] needs V * dim < 2^31.
 //   FAST math : a = (float)log(x) [glove] or (float)log(x/(1-x)) [pglove], b = f(x) weight
 //   JAVA math : a = x, b unused (log/pow are evaluated in fp64 inside the kernel)
 struct __align__(16) NzEntry {
@@ -79,10 +80,9 @@ struct __align__(16) NzEntry {
 #define GE_ID_BITS 27
 #define GE_ID_MASK 0x07ffffff
 #define GE_ID_KEEP ((int32_t)0x80000000)  // bit 31: row belongs to the L2-resident set (evict_last cache policy)
-// Damping exponent of an id that occurs `cnt` times where `hot_count` occurrences mean
-// GE_HOT_WRITERS expected concurrent writers: the smallest k >= 1 with cnt * 2^(-k/2) < hot_count
-// (capped at 15), so that the scaled deltas of all concurrent writers add up to between
-// GE_HOT_WRITERS / sqrt(2) and GE_HOT_WRITERS full steps.  0 = not a hub.
+// Concurrency class of an id that occurs `cnt` times where `hot_count` occurrences mean GE_HOT_WRITERS
+// expected concurrent writers: the smallest k >= 1 with cnt * 2^(-k/2) < hot_count (capped at 15), i.e.
+// cnt / hot_count lies in [2^((k-1)/2), 2^(k/2)).  0 = not a hub.
 __host__ __device__ inline int32_t ge_damp_bits(int32_t cnt, int32_t hot_count) {
     if (cnt < hot_count || hot_count <= 0) return 0;
     const int32_t k = (int32_t)floorf(2.0f * log2f((float)cnt / (float)hot_count)) + 1;
@@ -98,6 +98,8 @@ struct ge_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;      // stream all work is issued on (own_stream or the caller's)
     cudaStream_t own_stream = nullptr;
+    void* h_stage[2] = {nullptr, nullptr};        // pinned staging for pageable hand-off buffers (api.cu upload_staged)
+    cudaEvent_t ev_stage[2] = {nullptr, nullptr};
 
     // --- graph (A1) ---
     int32_t V = 0;
@@ -162,6 +164,9 @@ void ge_free_sim(ge_ctx* ctx);
 // api.cu
 void ge_free_graph(ge_ctx* ctx);
 int ge_graph_finish(ge_ctx* ctx);
+int ge_graph_alloc(ge_ctx* ctx, int32_t V, int64_t E_out, int64_t E_in);   // frees what depends on the old graph, allocates the CSR arrays
+int ge_graph_validate(ge_ctx* ctx);   // sorted / unique / in-range neighbour lists, monotone offsets (device pass)
+int upload_staged(ge_ctx* ctx, void* dst, const void* src, size_t bytes);   // pageable host -> device through pinned double buffers
 // bca.cu
 int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);
 void ge_free_cooc(ge_ctx* ctx);

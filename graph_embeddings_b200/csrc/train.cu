@@ -36,8 +36,9 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 // shuffled order, so under plain LRU a row survives between two of its visits only if it is touched
 // every ~50 us (C4: degree > ~19 000): the read hit rate is 13 % (profiles/r02_update_c4_ncu.md).
 // Rows whose occurrence count puts them among the ~60 000 most visited (bit 31 of the packed id, set
-// at pack time) are loaded and reduced with an evict_last cache policy, everything else with
-// evict_normal: the hot set then stays resident for the whole epoch.
+// at pack time) are loaded and reduced with an evict_last cache policy; everything else uses the
+// plain instructions (measured on B200: routing EVERY access through a createpolicy descriptor, even
+// evict_normal, costs 17 % at C4 — profiles/r02_l2_keep.md).
 __device__ __forceinline__ uint64_t l2_policy_keep() {
     uint64_t p;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
@@ -154,7 +155,7 @@ template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT, bool DYN>
 __global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
-                     int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
+                     int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf, float hot_w,
                      unsigned long long* __restrict__ queue, double* __restrict__ cost_out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -163,7 +164,7 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
     const double lr_d = (double)lr;
     double cost_d = 0.0;
     float cost_f = 0.0f;  // JAVA: the reference's f32 running cost (Adagrad.java:46,60)
-    const uint64_t pol_keep = l2_policy_keep(), pol_stream = l2_policy_stream();
+    const uint64_t pol_keep = l2_policy_keep();
 
     auto fetch = [&](int64_t pos) -> NzEntry {  // lane l fetches the nonzero at shuffled position pos
         NzEntry e = {0, 0, 0.f, 0.f};
@@ -226,15 +227,16 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             }
             int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
             int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
-            // bits 27..30 = damping exponent k of a hub id (pack time): its deltas are scaled by
-            // 2^(-k/2) so that the K stale steps the L2 adds up act like at most GE_HOT_WRITERS of them
-            float si = 1.f, sj = 1.f;
+            // bits 27..30 = concurrency class k of a hub id (pack time): about Ki = hot_w * 2^((k - 0.5) / 2) warps
+            // sit on that row at once, all reading the same stale state.  See the delta computation below.
+            float Ki = 0.f, Kj = 0.f;
             if (HOT) {  // HOT kernels exist for ATOMIC only
-                si = exp2f(-0.5f * (float)((bi >> GE_ID_BITS) & 15));
-                sj = exp2f(-0.5f * (float)((bj >> GE_ID_BITS) & 15));
+                const int ki = (bi >> GE_ID_BITS) & 15, kj = (bj >> GE_ID_BITS) & 15;
+                if (ki) Ki = hot_w * exp2f(0.5f * (float)ki - 0.25f);
+                if (kj) Kj = hot_w * exp2f(0.5f * (float)kj - 0.25f);
             }
-            // bit 31 = row is in the L2-resident set (pack time): warp-uniform choice of the cache policy
-            const uint64_t polw = bi < 0 ? pol_keep : pol_stream, polc = bj < 0 ? pol_keep : pol_stream;
+            // bit 31 = row is in the L2-resident set (pack time): warp-uniform choice of the access flavour
+            const bool keepw = bi < 0, keepc = bj < 0;
             bi &= GE_ID_MASK; bj &= GE_ID_MASK;
             const float ea = __shfl_sync(0xffffffffu, mine.a, t);
             const float eb = __shfl_sync(0xffffffffu, mine.b, t);
@@ -267,26 +269,27 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                 // measured on B200 (C3 graph): d=128 134.4 vs 141.8 ms, d=300 325 vs 370 ms per
                 // epoch; for rows narrower than a warp (d=100: 119.8 vs 107.7 ms) everything up
                 // front is faster, so the launcher picks by D4 (profiles/r01_load_order.md).
-                auto ldv = [&](float4 (&a)[NT], const float* base, float fill, uint64_t pol) {
+                auto ldv = [&](float4 (&a)[NT], const float* base, float fill, bool keep) {
 #pragma unroll
                     for (int q = 0; q < NT; q++) {
                         const int ch = lane + 32 * q;
-                        a[q] = ch < nchunk ? ldcg4p(base + 4 * ch, pol) : make_float4(fill, fill, fill, fill);
+                        a[q] = ch < nchunk ? (keep ? ldcg4p(base + 4 * ch, pol_keep) : ldcg4v(base + 4 * ch)) : make_float4(fill, fill, fill, fill);
                     }
                 };
-                ldv(w, wrow, 0.f, polw);
-                ldv(c, crow, 0.f, polc);
+                auto ldb = [&](const float* p, bool keep) -> float2 { return keep ? ldcg2p(p, pol_keep) : ldcg2v(p); };
+                ldv(w, wrow, 0.f, keepw);
+                ldv(c, crow, 0.f, keepc);
                 if (!two_phase) {
-                    ldv(gw, wrow + D4, 1.f, polw); ldv(gc, crow + D4, 1.f, polc);
-                    bw = ldcg2p(wrow + 2 * D4, polw); bc = ldcg2p(crow + 2 * D4, polc);
+                    ldv(gw, wrow + D4, 1.f, keepw); ldv(gc, crow + D4, 1.f, keepc);
+                    bw = ldb(wrow + 2 * D4, keepw); bc = ldb(crow + 2 * D4, keepc);
                 }
 #pragma unroll
                 for (int q = 0; q < NT; q++)
                     dot += w[q].x * c[q].x + w[q].y * c[q].y + w[q].z * c[q].z + w[q].w * c[q].w;
                 dot = warp_sum(dot);
                 if (two_phase) {
-                    ldv(gw, wrow + D4, 1.f, polw); ldv(gc, crow + D4, 1.f, polc);
-                    bw = ldcg2p(wrow + 2 * D4, polw); bc = ldcg2p(crow + 2 * D4, polc);
+                    ldv(gw, wrow + D4, 1.f, keepw); ldv(gc, crow + D4, 1.f, keepc);
+                    bw = ldb(wrow + 2 * D4, keepw); bc = ldb(crow + 2 * D4, keepc);
                 }
             }
 
@@ -330,8 +333,18 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         } else if (ATOMIC) {  // deltas, applied by the L2 with red.add
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
-                            float dw = -g1 * rsqrtf(gwv[e]) * lr, dc = -g2 * rsqrtf(gcv[e]) * lr;
-                            if (HOT) { dw *= si; dc *= sj; }  // gradsq keeps the full g^2, as every reference update adds it
+                            // K warps that all read gradsq = G and each ADD a step lr*g/sqrt(G) move the
+                            // parameter K*lr*g/sqrt(G); the reference's sequential updates would have seen G
+                            // grow by g^2 each time: sum_k lr*g/sqrt(G + k*g^2) ~ lr*(2/g)*(sqrt(G + K*g^2) - sqrt(G)).
+                            // The ratio of the two, 2 / (1 + sqrt(1 + K*g^2/G)), scales a hub id's delta: close
+                            // to 1/sqrt(K) while G is young (where K stale steps diverge), 1 once G >> K*g^2.
+                            // gradsq itself receives the full g^2 of every writer, as in the reference.
+                            const float a1 = g1 * rsqrtf(gwv[e]), a2 = g2 * rsqrtf(gcv[e]);
+                            float dw = -a1 * lr, dc = -a2 * lr;
+                            if (HOT) {
+                                dw *= __fdividef(2.f, 1.f + sqrtf(1.f + Ki * a1 * a1));
+                                dc *= __fdividef(2.f, 1.f + sqrtf(1.f + Kj * a2 * a2));
+                            }
                             wv[e] = dw;
                             cv[e] = dc;
                             gwv[e] = g1 * g1;
@@ -346,10 +359,20 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         }
                     }
                     if (ATOMIC) {
-                        red4p(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w, polw);
-                        red4p(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w, polw);
-                        red4p(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w, polc);
-                        red4p(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w, polc);
+                        if (keepw) {
+                            red4p(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w, pol_keep);
+                            red4p(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w, pol_keep);
+                        } else {
+                            red4(wrow + 4 * ch, w[q].x, w[q].y, w[q].z, w[q].w);
+                            red4(wrow + D4 + 4 * ch, gw[q].x, gw[q].y, gw[q].z, gw[q].w);
+                        }
+                        if (keepc) {
+                            red4p(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w, pol_keep);
+                            red4p(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w, pol_keep);
+                        } else {
+                            red4(crow + 4 * ch, c[q].x, c[q].y, c[q].z, c[q].w);
+                            red4(crow + D4 + 4 * ch, gc[q].x, gc[q].y, gc[q].z, gc[q].w);
+                        }
                     } else {
                         st4(wrow + 4 * ch, w[q]);
                         st4(crow + 4 * ch, c[q]);
@@ -366,8 +389,11 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
                 } else if (ATOMIC) {
-                    red2p(wrow + 2 * D4, -wc * rsqrtf(bw.y) * si, wc * wc, polw);
-                    red2p(crow + 2 * D4, -wc * rsqrtf(bc.y) * sj, wc * wc, polc);
+                    const float ab1 = wc * rsqrtf(bw.y), ab2 = wc * rsqrtf(bc.y);
+                    float s1 = 1.f, s2 = 1.f;
+                    if (HOT) { s1 = __fdividef(2.f, 1.f + sqrtf(1.f + Ki * ab1 * ab1)); s2 = __fdividef(2.f, 1.f + sqrtf(1.f + Kj * ab2 * ab2)); }
+                    if (keepw) red2p(wrow + 2 * D4, -ab1 * s1, wc * wc, pol_keep); else red2(wrow + 2 * D4, -ab1 * s1, wc * wc);
+                    if (keepc) red2p(crow + 2 * D4, -ab2 * s2, wc * wc, pol_keep); else red2(crow + 2 * D4, -ab2 * s2, wc * wc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
@@ -673,6 +699,8 @@ uint64_t epoch_key(int64_t seed, int32_t epoch) {
 // ==========================================================================================
 // host side
 // ==========================================================================================
+double ge_hot_writers();  // concurrent warps per id from which the stale-step correction applies (GE_HOT_WRITERS, default 16)
+
 // rows prefetched into L2 this many nonzeros ahead (GE_PF_DIST overrides; 0 = off; max 32)
 static int ge_prefetch_distance() {
     const char* e = getenv("GE_PF_DIST");  // read per launch: a development sweep can change it between epochs
@@ -745,6 +773,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                    : launch_adam_nt<false, false>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span);
     }
     const int pf = ge_prefetch_distance();
+    const float hot_w = (float)ge_hot_writers();
     const ge_config& c = ctx->cfg;
     // one instantiation per (NT, math, update mode, load order); grid = one resident wave
 #define GE_GO2(NT_, JAVA_, ATOMIC_, TP_, HOT_, DYN_)                                                      \
@@ -754,7 +783,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
         if (c.serial) { block = dim3(32); grid = dim3(1); }                                               \
         else grid = wave_grid(ctx, k, count, span);                                                       \
         k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax,       \
-                                  c.learning_rate, pf, queue, d_cost);                                    \
+                                  c.learning_rate, pf, hot_w, queue, d_cost);                             \
     }
 #define GE_GO(NT_, JAVA_, ATOMIC_, TP_, HOT_)                                                             \
     {                                                                                                     \
@@ -911,8 +940,10 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 // (Adagrad.java:76-80).  Hot ids get a damping exponent (common.cuh ge_damp_bits) that scales their
 // deltas so the sum stays below GE_HOT_WRITERS full steps.  Returns the occurrence count from which
 // an id is hot.
+double ge_hot_writers() { return getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0; }
+
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
-    const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
+    const double writers = ge_hot_writers();
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
     if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
     if (warps < 1) warps = 1;
