@@ -91,6 +91,8 @@ SIGNATURES = {
     "ge_dist_prepare": (C.c_int, [_P, _I32]),
     "ge_dist_train_epoch": (C.c_int, [_P, C.POINTER(_F64)]),
     "ge_dist_extract_f32": (C.c_int, [_P, _P, _I64]),
+    "ge_dist_extract": (C.c_int, [_P, _P, _I64]),
+    "ge_dist_set_graph_csr": (C.c_int, [_P, _I32, _I32, _P, _P, _P, _P, _P, _P]),
     "ge_dist_stats": (C.c_int, [_P, _P, _I32, C.POINTER(_F64), C.POINTER(_I64)]),
     "ge_dist_rotation_mode": (C.c_int, [_P]),
 }

@@ -97,7 +97,8 @@ int upload_staged(ge_ctx* ctx, void* dst, const void* src, size_t bytes) {
     for (size_t c = 0; c < n; c++) {
         const int b = (int)(c & 1);
         const size_t o = c * chunk, len = bytes - o < chunk ? bytes - o : chunk;
-        if (c >= 2) GE_CUDA(cudaEventSynchronize(ctx->ev_stage[b]));  // the copy out of this buffer two chunks ago is done
+        // the copy out of this buffer (two chunks ago, or the tail of the previous upload) must be done
+        if (ctx->stage_busy[b]) { GE_CUDA(cudaEventSynchronize(ctx->ev_stage[b])); ctx->stage_busy[b] = false; }
         char* h = (char*)ctx->h_stage[b];
         const char* sp = (const char*)src + o;
         std::vector<std::thread> th;
@@ -108,6 +109,7 @@ int upload_staged(ge_ctx* ctx, void* dst, const void* src, size_t bytes) {
         for (auto& x : th) x.join();
         GE_CUDA(cudaMemcpyAsync((char*)dst + o, h, len, cudaMemcpyHostToDevice, st));
         GE_CUDA(cudaEventRecord(ctx->ev_stage[b], st));
+        ctx->stage_busy[b] = true;
     }
     return GE_OK;
 }

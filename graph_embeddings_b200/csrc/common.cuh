@@ -100,6 +100,7 @@ struct ge_ctx {
     cudaStream_t own_stream = nullptr;
     void* h_stage[2] = {nullptr, nullptr};        // pinned staging for pageable hand-off buffers (api.cu upload_staged)
     cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+    bool stage_busy[2] = {false, false};          // a copy out of the staging buffer may still be in flight
 
     // --- graph (A1) ---
     int32_t V = 0;
@@ -153,6 +154,9 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                      bool any_hot /* some entries carry hub damping exponents: use the HOT kernel variant */,
                      unsigned long long* queue /* zeroed device counter: dynamic batch claiming; nullptr = static */);
 void ge_free_store(ge_ctx* ctx);
+// (W + C) / 2 of `nblocks` slab pairs, rows[k] rows each, concatenated into host memory through pinned double buffers
+template <typename T>
+int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (damped deltas)
 void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i, const int32_t* cnt_j, int64_t nj,

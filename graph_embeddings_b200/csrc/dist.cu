@@ -190,23 +190,6 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
     }
 }
 
-template <typename T>
-__global__ void dist_extract(const float* __restrict__ W, const float* __restrict__ C, int32_t rows, int32_t dim,
-                             int32_t S, T* __restrict__ out) {
-    const int64_t total = (int64_t)rows * dim, stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
-        const int64_t r = k / dim;
-        const int32_t d = (int32_t)(k - r * dim);
-        out[k] = (T)__fdiv_rn(__fadd_rn(W[r * S + d], C[r * S + d]), 2.0f);
-    }
-}
-
-}  // namespace
-
-
-
-namespace {
-
 struct IpcPair { cudaIpcMemHandle_t ring; int32_t ok; int32_t pad[15]; };
 
 void dist_unmap_peers(DistState* d) {
@@ -594,31 +577,75 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     return GE_OK;
 }
 
-// (W + C)/2 for this rank's id range; valid between epochs, when every C block is home
-extern "C" int ge_dist_extract_f32(ge_ctx* ctx, float* out, int64_t cap) {
+// (W + C)/2 for this rank's id range; valid between epochs, when every C block is home.  Same pinned
+// double-buffered path as ge_extract (train.cu).
+template <typename T>
+static int dist_extract_impl(ge_ctx* ctx, T* out, int64_t cap) {
     if (!ctx || !ctx->dist || !ctx->have_store) { if (ctx) ctx->err = "ge_dist_prepare first"; return GE_ERR_STATE; }
     DistState* d = ctx->dist;
     const int32_t dim = ctx->cfg.dim;
-    if (cap < (int64_t)d->row_cnt * dim) { ctx->err = "extract capacity too small"; return GE_ERR_INVALID; }
+    if (!out || cap < (int64_t)d->row_cnt * dim) { ctx->err = "extract capacity too small"; return GE_ERR_INVALID; }
     cudaSetDevice(ctx->cfg.device);
-    cudaStream_t st = ctx->stream;
     const size_t slab = (size_t)d->Bs * ctx->S;
     const int slots = d->world > 1 ? d->m + 1 : d->m;
-    float* tmp = nullptr;
-    GE_CUDA(cudaMalloc(&tmp, (size_t)d->Bs * dim * sizeof(float)));
+    std::vector<const float*> W, C;
+    std::vector<int64_t> rows;
     for (int k = 0; k < d->m; k++) {
-        const int64_t r0 = (int64_t)k * d->Bs;
-        int64_t rows = (int64_t)d->row_cnt - r0;
-        if (rows <= 0) break;
-        if (rows > d->Bs) rows = d->Bs;
-        const float* Cslot = d->d_Cring + (size_t)((d->head + k) % slots) * slab;
-        dist_extract<float><<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_W + (size_t)k * slab, Cslot, (int32_t)rows, dim, ctx->S, tmp);
-        cudaError_t e = cudaMemcpyAsync(out + r0 * dim, tmp, (size_t)rows * dim * sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) { cudaFree(tmp); GE_CUDA(e); }
+        int64_t n = (int64_t)d->row_cnt - (int64_t)k * d->Bs;
+        if (n <= 0) break;
+        if (n > d->Bs) n = d->Bs;
+        W.push_back(ctx->d_W + (size_t)k * slab);
+        C.push_back(d->d_Cring + (size_t)((d->head + k) % slots) * slab);
+        rows.push_back(n);
     }
-    cudaFree(tmp);
-    return GE_OK;
+    return ge_extract_blocks<T>(ctx, (int)rows.size(), W.data(), C.data(), rows.data(), out);
+}
+extern "C" int ge_dist_extract_f32(ge_ctx* ctx, float* out, int64_t cap) { return dist_extract_impl<float>(ctx, out, cap); }
+extern "C" int ge_dist_extract(ge_ctx* ctx, double* out, int64_t cap) { return dist_extract_impl<double>(ctx, out, cap); }
+
+// A1 hand-off for N ranks: ONE host -> device copy on `root`, then ncclBroadcast of the six CSR arrays over
+// NVLink, instead of N uploads of the same graph across PCIe.  Non-root ranks pass V = 0 and null arrays.
+extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const int64_t* out_off, const int32_t* out_nbr,
+                                     const float* out_w, const int64_t* in_off, const int32_t* in_nbr, const float* in_w) {
+    if (!ctx || !ctx->dist) { if (ctx) ctx->err = "ge_dist_init first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    if (d->world == 1) return ge_set_graph_csr(ctx, V, out_off, out_nbr, out_w, in_off, in_nbr, in_w);
+    if (root < 0 || root >= d->world) { ctx->err = "bad root"; return GE_ERR_INVALID; }
+    const bool me = d->rank == root;
+    cudaSetDevice(ctx->cfg.device);
+    cudaStream_t st = ctx->stream;
+    long long hdr[4] = {0, 0, 0, 0};  // V, E_out, E_in, ok
+    if (me) {
+        const bool ok = V > 0 && out_off && in_off && out_off[V] >= 0 && in_off[V] >= 0 &&
+                        (out_off[V] == 0 || (out_nbr && out_w)) && (in_off[V] == 0 || (in_nbr && in_w));
+        hdr[0] = V; hdr[1] = ok ? out_off[V] : 0; hdr[2] = ok ? in_off[V] : 0; hdr[3] = ok;
+    }
+    long long* d_hdr = nullptr;
+    GE_CUDA(cudaMalloc(&d_hdr, sizeof(hdr)));
+    cudaError_t e = cudaMemcpyAsync(d_hdr, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st);
+    int nr = e == cudaSuccess ? g_nccl.Broadcast(d_hdr, d_hdr, sizeof(hdr), NCCL_UINT8, root, d->comm, st) : 0;
+    if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(hdr, d_hdr, sizeof(hdr), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
+    cudaFree(d_hdr);
+    GE_CUDA(e);
+    GE_NCCL(nr);
+    if (!hdr[3]) { ctx->err = "bad graph arguments on the root rank"; return GE_ERR_INVALID; }
+    int r = ge_graph_alloc(ctx, (int32_t)hdr[0], hdr[1], hdr[2]);
+    if (r) { ge_free_graph(ctx); return r; }
+    const size_t ob = (size_t)(ctx->V + 1) * sizeof(int64_t);
+    const struct { void* dv; const void* h; size_t n; } parts[] = {
+        {ctx->d_out_off, out_off, ob}, {ctx->d_in_off, in_off, ob},
+        {ctx->d_out_nbr, out_nbr, (size_t)ctx->E_out * 4}, {ctx->d_out_w, out_w, (size_t)ctx->E_out * 4},
+        {ctx->d_in_nbr, in_nbr, (size_t)ctx->E_in * 4}, {ctx->d_in_w, in_w, (size_t)ctx->E_in * 4}};
+    for (const auto& q : parts) {
+        if (!q.n) continue;
+        if (me) { r = upload_staged(ctx, q.dv, q.h, q.n); if (r) { ge_free_graph(ctx); return r; } }
+        GE_NCCL(g_nccl.Broadcast(q.dv, q.dv, q.n, NCCL_UINT8, root, d->comm, st));
+    }
+    ctx->graph_seconds = 0;
+    r = ge_graph_validate(ctx);
+    if (r) return r;
+    return ge_graph_finish(ctx);
 }
 
 // data plane of the rotation actually in use: 0 = NCCL send/recv in the compute stream, 1 = half-block

@@ -155,7 +155,7 @@ template <int NT, bool JAVA, bool ATOMIC, bool TP, bool HOT, bool DYN>
 __global__ void __launch_bounds__(256, (NT == 1 && !JAVA) ? 4 : 1)
 glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __restrict__ W,
                      float* __restrict__ C, const int32_t* __restrict__ perm, Bijection bij,
-                     int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf, float hot_w,
+                     int32_t D4, int32_t S, int32_t method, double xmax, float lr, int32_t pf,
                      unsigned long long* __restrict__ queue, double* __restrict__ cost_out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -227,13 +227,12 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
             }
             int32_t bi = __shfl_sync(0xffffffffu, mine.i, t);
             int32_t bj = __shfl_sync(0xffffffffu, mine.j, t);
-            // bits 27..30 = concurrency class k of a hub id (pack time): about Ki = hot_w * 2^((k - 0.5) / 2) warps
-            // sit on that row at once, all reading the same stale state.  See the delta computation below.
-            float Ki = 0.f, Kj = 0.f;
+            // bits 27..30 = concurrency class k of a hub id (pack time): its deltas are scaled by 2^(-k/2)
+            // so that the K stale steps the L2 adds up act like at most GE_HOT_WRITERS of them
+            float si = 1.f, sj = 1.f;
             if (HOT) {  // HOT kernels exist for ATOMIC only
-                const int ki = (bi >> GE_ID_BITS) & 15, kj = (bj >> GE_ID_BITS) & 15;
-                if (ki) Ki = hot_w * exp2f(0.5f * (float)ki - 0.25f);
-                if (kj) Kj = hot_w * exp2f(0.5f * (float)kj - 0.25f);
+                si = exp2f(-0.5f * (float)((bi >> GE_ID_BITS) & 15));
+                sj = exp2f(-0.5f * (float)((bj >> GE_ID_BITS) & 15));
             }
             // bit 31 = row is in the L2-resident set (pack time): warp-uniform choice of the access flavour
             const bool keepw = bi < 0, keepc = bj < 0;
@@ -333,18 +332,12 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                         } else if (ATOMIC) {  // deltas, applied by the L2 with red.add
                             const float g1 = wc * cv[e];
                             const float g2 = wc * wv[e];
-                            // K warps that all read gradsq = G and each ADD a step lr*g/sqrt(G) move the
-                            // parameter K*lr*g/sqrt(G); the reference's sequential updates would have seen G
-                            // grow by g^2 each time: sum_k lr*g/sqrt(G + k*g^2) ~ lr*(2/g)*(sqrt(G + K*g^2) - sqrt(G)).
-                            // The ratio of the two, 2 / (1 + sqrt(1 + K*g^2/G)), scales a hub id's delta: close
-                            // to 1/sqrt(K) while G is young (where K stale steps diverge), 1 once G >> K*g^2.
-                            // gradsq itself receives the full g^2 of every writer, as in the reference.
-                            const float a1 = g1 * rsqrtf(gwv[e]), a2 = g2 * rsqrtf(gcv[e]);
-                            float dw = -a1 * lr, dc = -a2 * lr;
-                            if (HOT) {
-                                dw *= __fdividef(2.f, 1.f + sqrtf(1.f + Ki * a1 * a1));
-                                dc *= __fdividef(2.f, 1.f + sqrtf(1.f + Kj * a2 * a2));
-                            }
+                            float dw = -g1 * rsqrtf(gwv[e]) * lr, dc = -g2 * rsqrtf(gcv[e]) * lr;
+                            // gradsq keeps the full g^2, as every reference update adds it.  (A state-dependent
+                            // factor 2 / (1 + sqrt(1 + K g^2 / G)) — the exact ratio for K equal stale AdaGrad
+                            // steps — was measured instead of the constant: better late epochs, but it ignores the
+                            // curvature of the bias step and diverged inside column blocks; profiles/r02_hubs.md.)
+                            if (HOT) { dw *= si; dc *= sj; }
                             wv[e] = dw;
                             cv[e] = dc;
                             gwv[e] = g1 * g1;
@@ -389,11 +382,9 @@ glove_adagrad_update(const NzEntry* __restrict__ nz, int64_t count, float* __res
                     bw.y = __fadd_rn(bw.y, w2);
                     bc.y = __fadd_rn(bc.y, w2);
                 } else if (ATOMIC) {
-                    const float ab1 = wc * rsqrtf(bw.y), ab2 = wc * rsqrtf(bc.y);
-                    float s1 = 1.f, s2 = 1.f;
-                    if (HOT) { s1 = __fdividef(2.f, 1.f + sqrtf(1.f + Ki * ab1 * ab1)); s2 = __fdividef(2.f, 1.f + sqrtf(1.f + Kj * ab2 * ab2)); }
-                    if (keepw) red2p(wrow + 2 * D4, -ab1 * s1, wc * wc, pol_keep); else red2(wrow + 2 * D4, -ab1 * s1, wc * wc);
-                    if (keepc) red2p(crow + 2 * D4, -ab2 * s2, wc * wc, pol_keep); else red2(crow + 2 * D4, -ab2 * s2, wc * wc);
+                    const float ab1 = wc * rsqrtf(bw.y) * si, ab2 = wc * rsqrtf(bc.y) * sj;
+                    if (keepw) red2p(wrow + 2 * D4, -ab1, wc * wc, pol_keep); else red2(wrow + 2 * D4, -ab1, wc * wc);
+                    if (keepc) red2p(crow + 2 * D4, -ab2, wc * wc, pol_keep); else red2(crow + 2 * D4, -ab2, wc * wc);
                 } else {
                     bw.x -= wc * rsqrtf(bw.y);
                     bc.x -= wc * rsqrtf(bc.y);
@@ -699,8 +690,6 @@ uint64_t epoch_key(int64_t seed, int32_t epoch) {
 // ==========================================================================================
 // host side
 // ==========================================================================================
-double ge_hot_writers();  // concurrent warps per id from which the stale-step correction applies (GE_HOT_WRITERS, default 16)
-
 // rows prefetched into L2 this many nonzeros ahead (GE_PF_DIST overrides; 0 = off; max 32)
 static int ge_prefetch_distance() {
     const char* e = getenv("GE_PF_DIST");  // read per launch: a development sweep can change it between epochs
@@ -773,7 +762,6 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
                    : launch_adam_nt<false, false>(ctx, nt, st, nz, count, W, C, perm, bij, d_cost, span);
     }
     const int pf = ge_prefetch_distance();
-    const float hot_w = (float)ge_hot_writers();
     const ge_config& c = ctx->cfg;
     // one instantiation per (NT, math, update mode, load order); grid = one resident wave
 #define GE_GO2(NT_, JAVA_, ATOMIC_, TP_, HOT_, DYN_)                                                      \
@@ -783,7 +771,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
         if (c.serial) { block = dim3(32); grid = dim3(1); }                                               \
         else grid = wave_grid(ctx, k, count, span);                                                       \
         k<<<grid, block, 0, st>>>(nz, count, W, C, perm, bij, ctx->D4, ctx->S, c.method, ctx->xmax,       \
-                                  c.learning_rate, pf, hot_w, queue, d_cost);                             \
+                                  c.learning_rate, pf, queue, d_cost);                                    \
     }
 #define GE_GO(NT_, JAVA_, ATOMIC_, TP_, HOT_)                                                             \
     {                                                                                                     \
@@ -940,10 +928,8 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 // (Adagrad.java:76-80).  Hot ids get a damping exponent (common.cuh ge_damp_bits) that scales their
 // deltas so the sum stays below GE_HOT_WRITERS full steps.  Returns the occurrence count from which
 // an id is hot.
-double ge_hot_writers() { return getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0; }
-
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
-    const double writers = ge_hot_writers();
+    const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
     if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
     if (warps < 1) warps = 1;
@@ -1060,68 +1046,109 @@ extern "C" int ge_cost_history(ge_ctx* ctx, double* out, int32_t cap) {
 // The result goes to pageable host memory (a Java double[] / numpy array), which the driver would
 // copy at 3-4 GB/s through its own staging.  Instead: row chunks through two pinned staging buffers;
 // while chunk c crosses PCIe, host threads move chunk c-1 from staging into `out` (they also take the
-// first-touch page faults of a freshly allocated destination in parallel).
-template <typename T>
-static int extract_impl(ge_ctx* ctx, T* out) {
-    if (!ctx || !out) return GE_ERR_INVALID;
-    if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
-    const int32_t V = ctx->V, dim = ctx->cfg.dim;
-    const size_t row_bytes = (size_t)dim * sizeof(T);
-    int64_t chunk_rows = (int64_t)((size_t)(48u << 20) / row_bytes);
-    if (chunk_rows < 1) chunk_rows = 1;
-    if (chunk_rows > V) chunk_rows = V;
-    const size_t chunk_bytes = (size_t)chunk_rows * row_bytes;
-    T *d[2] = {nullptr, nullptr}, *h[2] = {nullptr, nullptr};
+// first-touch page faults of a freshly allocated destination in parallel).  The device always produces
+// f32 — (float)(f + c) / 2 IS the reference's value (Optimizer.java:130-140) — and the widening to the
+// double[] the seam returns happens in that host pass: half the PCIe bytes, identical bits.
+struct ExtractStage {
+    float* d[2] = {nullptr, nullptr};
+    float* h[2] = {nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
-    cudaError_t e = cudaSuccess;
-    for (int k = 0; k < 2 && e == cudaSuccess; k++) {
-        e = cudaMalloc(&d[k], chunk_bytes);
-        if (e == cudaSuccess) e = cudaMallocHost(&h[k], chunk_bytes);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+    int64_t chunk_rows = 0;
+    cudaError_t init(int32_t dim, int64_t max_rows) {
+        chunk_rows = (int64_t)((size_t)(48u << 20) / ((size_t)dim * sizeof(float)));
+        if (chunk_rows < 1) chunk_rows = 1;
+        if (chunk_rows > max_rows) chunk_rows = max_rows > 0 ? max_rows : 1;
+        cudaError_t e = cudaSuccess;
+        for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+            e = cudaMalloc(&d[k], (size_t)chunk_rows * dim * sizeof(float));
+            if (e == cudaSuccess) e = cudaMallocHost(&h[k], (size_t)chunk_rows * dim * sizeof(float));
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+        }
+        return e;
     }
+    ~ExtractStage() {
+        for (int k = 0; k < 2; k++) {
+            cudaFree(d[k]);
+            cudaFreeHost(h[k]);
+            if (ev[k]) cudaEventDestroy(ev[k]);
+        }
+    }
+};
+
+// rows [0, rows) of the slabs W / C -> out (rows x dim, row-major)
+template <typename T>
+static cudaError_t extract_rows(ge_ctx* ctx, ExtractStage& S, const float* W, const float* C, int64_t rows, T* out) {
+    const int32_t dim = ctx->cfg.dim;
     unsigned nthr = std::thread::hardware_concurrency();
     nthr = nthr < 1 ? 1 : (nthr > 8 ? 8 : nthr);
     auto drain = [&](int64_t c) {  // chunk c: staging -> out
-        const int64_t row0 = c * chunk_rows;
-        const size_t bytes = (size_t)((V - row0) < chunk_rows ? (V - row0) : chunk_rows) * row_bytes;
-        const char* src = (const char*)h[c & 1];
-        char* dst = (char*)out + (size_t)row0 * row_bytes;
-        if (bytes < (8u << 20) || nthr == 1) { memcpy(dst, src, bytes); return; }
+        const int64_t row0 = c * S.chunk_rows;
+        const size_t n = (size_t)((rows - row0) < S.chunk_rows ? (rows - row0) : S.chunk_rows) * dim;
+        const float* src = S.h[c & 1];
+        T* dst = out + (size_t)row0 * dim;
+        auto move = [=](size_t lo, size_t hi) {
+            if (sizeof(T) == sizeof(float)) memcpy((void*)(dst + lo), src + lo, (hi - lo) * sizeof(float));
+            else for (size_t k = lo; k < hi; k++) dst[k] = (T)src[k];
+        };
+        if (n < ((size_t)2 << 20) || nthr == 1) { move(0, n); return; }
         std::vector<std::thread> th;
-        for (unsigned t = 0; t < nthr; t++) {
-            const size_t lo = bytes * t / nthr, hi = bytes * (t + 1) / nthr;
-            th.emplace_back([=] { memcpy(dst + lo, src + lo, hi - lo); });
-        }
+        for (unsigned t = 0; t < nthr; t++) th.emplace_back(move, n * t / nthr, n * (t + 1) / nthr);
         for (auto& x : th) x.join();
     };
-    const int64_t nchunk = (V + chunk_rows - 1) / chunk_rows;
+    const int64_t nchunk = (rows + S.chunk_rows - 1) / S.chunk_rows;
+    cudaError_t e = cudaSuccess;
     for (int64_t c = 0; c < nchunk && e == cudaSuccess; c++) {
-        const int64_t row0 = c * chunk_rows;
-        const int32_t rows = (int32_t)((V - row0) < chunk_rows ? (V - row0) : chunk_rows);
+        const int64_t row0 = c * S.chunk_rows;
+        const int32_t nr = (int32_t)((rows - row0) < S.chunk_rows ? (rows - row0) : S.chunk_rows);
         // slot c&1 was drained two iterations ago (drain runs on this thread), so it is free
-        extract_avg<T><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_W, ctx->d_C, row0, rows, dim, ctx->S, d[c & 1]);
-        e = cudaMemcpyAsync(h[c & 1], d[c & 1], (size_t)rows * row_bytes, cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaEventRecord(ev[c & 1], ctx->stream);
+        extract_avg<float><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(W, C, row0, nr, dim, ctx->S, S.d[c & 1]);
+        e = cudaMemcpyAsync(S.h[c & 1], S.d[c & 1], (size_t)nr * dim * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(S.ev[c & 1], ctx->stream);
         if (c > 0 && e == cudaSuccess) {
-            e = cudaEventSynchronize(ev[(c - 1) & 1]);
+            e = cudaEventSynchronize(S.ev[(c - 1) & 1]);
             if (e == cudaSuccess) drain(c - 1);
         }
     }
     if (e == cudaSuccess && nchunk > 0) {
-        e = cudaEventSynchronize(ev[(nchunk - 1) & 1]);
+        e = cudaEventSynchronize(S.ev[(nchunk - 1) & 1]);
         if (e == cudaSuccess) drain(nchunk - 1);
     }
+    return e;
+}
+
+template <typename T>
+static int extract_impl(ge_ctx* ctx, T* out) {
+    if (!ctx || !out) return GE_ERR_INVALID;
+    if (!ctx->have_store) { ctx->err = "no embedding store"; return GE_ERR_STATE; }
+    if (ctx->dist) { ctx->err = "block-rotation trainer: use ge_dist_extract / ge_dist_extract_f32"; return GE_ERR_STATE; }
+    cudaSetDevice(ctx->cfg.device);
+    ExtractStage S;
+    cudaError_t e = S.init(ctx->cfg.dim, ctx->V);
+    if (e == cudaSuccess) e = extract_rows<T>(ctx, S, ctx->d_W, ctx->d_C, ctx->V, out);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    for (int k = 0; k < 2; k++) {
-        cudaFree(d[k]);
-        cudaFreeHost(h[k]);
-        if (ev[k]) cudaEventDestroy(ev[k]);
-    }
     GE_CUDA(e);
     return GE_OK;
 }
 extern "C" int ge_extract(ge_ctx* ctx, double* out) { return extract_impl<double>(ctx, out); }
 extern "C" int ge_extract_f32(ge_ctx* ctx, float* out) { return extract_impl<float>(ctx, out); }
+
+// block trainer (dist.cu): `nblocks` (W slab, C slab) pairs of `rows[k]` rows each, concatenated into out
+template <typename T>
+int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out) {
+    int64_t mx = 1;
+    for (int k = 0; k < nblocks; k++) mx = rows[k] > mx ? rows[k] : mx;
+    ExtractStage S;
+    cudaError_t e = S.init(ctx->cfg.dim, mx);
+    for (int k = 0; k < nblocks && e == cudaSuccess; k++) {
+        e = extract_rows<T>(ctx, S, W[k], C[k], rows[k], out);
+        out += (size_t)rows[k] * ctx->cfg.dim;
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    GE_CUDA(e);
+    return GE_OK;
+}
+template int ge_extract_blocks<float>(ge_ctx*, int, const float* const*, const float* const*, const int64_t*, float*);
+template int ge_extract_blocks<double>(ge_ctx*, int, const float* const*, const float* const*, const int64_t*, double*);
 
 extern "C" int ge_store_export(ge_ctx* ctx, int32_t which, float* out) {
     if (!ctx || !out || which < 0 || which > 11) return GE_ERR_INVALID;

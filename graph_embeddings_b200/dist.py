@@ -32,15 +32,25 @@ class DistTrainer:
         self._n.ck(self._n.L.ge_dist_row_range(self._n.h, V, self.nb, C.byref(f), C.byref(c)))
         return f.value, c.value
 
-    def build(self, graph):
-        """replicate the CSR, build this rank's co-occurrence rows (bookmarks are independent)."""
+    def build(self, graph, root: int | None = None):
+        """hand the CSR to every rank, build this rank's co-occurrence rows (bookmarks are independent).
+        root = None: every rank uploads its own host copy; root = r: only rank r's arrays are read (one
+        H2D there + ncclBroadcast over NVLink), the other ranks may pass graph = None."""
         n, L, g = self._n, self._n.L, graph
-        arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
-                np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
-                np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
-        n.ck(L.ge_set_graph_csr(n.h, g.V, *map(_ptr, arrs)))
-        self.V = g.V
-        first, count = self.row_range(g.V)
+        if root is None or self.world == 1:
+            arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
+                    np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
+                    np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
+            n.ck(L.ge_set_graph_csr(n.h, g.V, *map(_ptr, arrs)))
+        elif self.rank == root:
+            arrs = [np.ascontiguousarray(g.out_off, np.int64), np.ascontiguousarray(g.out_nbr, np.int32),
+                    np.ascontiguousarray(g.out_w, np.float32), np.ascontiguousarray(g.in_off, np.int64),
+                    np.ascontiguousarray(g.in_nbr, np.int32), np.ascontiguousarray(g.in_w, np.float32)]
+            n.ck(L.ge_dist_set_graph_csr(n.h, root, g.V, *map(_ptr, arrs)))
+        else:
+            n.ck(L.ge_dist_set_graph_csr(n.h, root, 0, None, None, None, None, None, None))
+        self.V = L.ge_vocab_size(n.h)
+        first, count = self.row_range(self.V)
         nnz, xmax = C.c_int64(0), C.c_double(0)
         n.ck(L.ge_cooc_build_rows(n.h, first, count, C.byref(nnz), C.byref(xmax)))
         return nnz.value, xmax.value
@@ -68,6 +78,13 @@ class DistTrainer:
         _, count = self.row_range(self.V)
         out = np.empty((count, self.config.dim), np.float32)
         self._n.ck(self._n.L.ge_dist_extract_f32(self._n.h, _ptr(out), out.size))
+        return out
+
+    def extract_local_f64(self) -> np.ndarray:
+        """this rank's rows of Optimum.getResult(): double[count * dim] as the seam returns it"""
+        _, count = self.row_range(self.V)
+        out = np.empty((count, self.config.dim), np.float64)
+        self._n.ck(self._n.L.ge_dist_extract(self._n.h, _ptr(out), out.size))
         return out
 
     def stats(self):

@@ -264,8 +264,13 @@ int ge_dist_prepare(ge_ctx*, int32_t nblocks);
 /* one epoch = nblocks sub-epochs, each followed by the ring rotation of one C block
  * (ncclSend to rank-1 / ncclRecv from rank+1); cost = global localCost (all-reduced) */
 int ge_dist_train_epoch(ge_ctx*, double* cost);
-/* (W+C)/2 of this rank's id range, row-major count x dim */
+/* (W+C)/2 of this rank's id range, row-major count x dim (f64: what extractResult() returns, Optimizer.java:130-140) */
 int ge_dist_extract_f32(ge_ctx*, float* out, int64_t cap);
+int ge_dist_extract(ge_ctx*, double* out, int64_t cap);
+/* A1 hand-off for N ranks: one host -> device copy on `root` + ncclBroadcast of the CSR arrays over NVLink instead
+ * of N uploads across PCIe.  Non-root ranks pass V = 0 and NULL arrays.  world == 1: same as ge_set_graph_csr. */
+int ge_dist_set_graph_csr(ge_ctx*, int32_t root, int32_t V, const int64_t* out_off, const int32_t* out_nbr,
+                          const float* out_w, const int64_t* in_off, const int32_t* in_nbr, const float* in_w);
 /* data plane of the rotation in use: 2 = half blocks pushed by the copy engine into the neighbour's ring
  * (CUDA IPC mapping, flag hand-shake with stream memory operations; default), 1 = half-block
  * ncclSend/ncclRecv on a second stream (GE_DIST_ROT=pipe, or the fallback when IPC is unavailable),
