@@ -225,6 +225,9 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     ge_free_graph(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->hub_stream) cudaStreamDestroy(ctx->hub_stream);
     for (int k = 0; k < 2; k++) {
         if (ctx->h_stage[k]) cudaFreeHost(ctx->h_stage[k]);
         if (ctx->ev_stage[k]) cudaEventDestroy(ctx->ev_stage[k]);

@@ -136,6 +136,12 @@ struct ge_ctx {
     double* d_cost = nullptr;     // epoch cost accumulator
     bool any_hot = false;         // packed nonzeros carry hub damping exponents
     int32_t keep_count = 0x7fffffff;  // ids occurring at least this often are in the L2-resident set
+    // packed array = [cold nonzeros | nonzeros touching an extreme hub]; the second segment has its own launch
+    int64_t n_cold = 0, hub_warps = 0;
+    cudaStream_t hub_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int64_t launch_max_warps = 0, launch_reserve_blocks = 0;  // per-launch overrides (train.cu shape_launch)
+    int32_t launch_pf = -1;
     int32_t epoch = 0;
     std::vector<double> history;
     double update_seconds = 0;
