@@ -221,7 +221,9 @@ class BookmarkColoring(CoOccurrenceMatrix):
     def stats(self):
         pops, scanned, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
         self._n.ck(self._n.L.ge_cooc_stats(self._n.h, C.byref(pops), C.byref(scanned), C.byref(sec)))
-        return {"pops": pops.value, "scanned": scanned.value, "seconds": sec.value, "nnz": self._nnz}
+        fetched = C.c_int64(0)
+        self._n.ck(self._n.L.ge_cooc_fetched(self._n.h, C.byref(fetched)))
+        return {"pops": pops.value, "scanned": scanned.value, "fetched": fetched.value, "seconds": sec.value, "nnz": self._nnz}
 
     def graph_csr(self):
         """The hand-off CSR as it sits on the device (validation of ge_set_graph_edges):
@@ -335,7 +337,10 @@ class Adagrad(IOptimizer):
     def stats(self):
         s, l, u = C.c_double(0), C.c_int64(0), C.c_int64(0)
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
-        return {"update_seconds": s.value, "launches": l.value, "updates": u.value}
+        k, n, w = C.c_double(0), C.c_int32(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(n), C.byref(w)))
+        return {"update_seconds": s.value, "launches": l.value, "updates": u.value,
+                "hub": {"max_concurrency": k.value, "capped_launches": n.value, "warp_cap": w.value}}
 
     def reset(self):
         """A fresh optimizer on the same matrix (new Adagrad(coMatrix, ...), Main.java:72): store

@@ -225,9 +225,6 @@ extern "C" void ge_destroy(ge_ctx* ctx) {
     ge_free_graph(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
-    if (ctx->hub_stream) cudaStreamDestroy(ctx->hub_stream);
     for (int k = 0; k < 2; k++) {
         if (ctx->h_stage[k]) cudaFreeHost(ctx->h_stage[k]);
         if (ctx->ev_stage[k]) cudaEventDestroy(ctx->ev_stage[k]);
@@ -334,6 +331,12 @@ extern "C" int ge_cooc_stats(ge_ctx* ctx, int64_t* pops, int64_t* scanned, doubl
     if (pops) *pops = ctx->bca_pops;
     if (scanned) *scanned = ctx->bca_scanned;
     if (seconds) *seconds = ctx->bca_seconds;
+    return GE_OK;
+}
+
+extern "C" int ge_cooc_fetched(ge_ctx* ctx, int64_t* fetched) {
+    if (!ctx || !fetched) return GE_ERR_INVALID;
+    *fetched = ctx->bca_fetched;
     return GE_OK;
 }
 

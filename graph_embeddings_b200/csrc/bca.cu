@@ -60,7 +60,7 @@ struct BcaParams {
     int32_t* overflow; int32_t* n_overflow;   // table too small -> next tier
     int32_t* deferred; int32_t* n_deferred;   // arena full -> next arena
     int32_t* gmax_bits;                       // global max (non-negative float as int)
-    unsigned long long *pops, *scanned;
+    unsigned long long *pops, *scanned, *fetched;
 };
 
 __device__ __forceinline__ uint16_t cas_slot(uint16_t* a, uint16_t v) {
@@ -105,7 +105,7 @@ struct Table {
 // on table T holding n records; returns the new n, or -1 on table overflow.
 template <typename HT>
 __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int lane, int& npop,
-                        unsigned long long& pops, unsigned long long& scanned) {
+                        unsigned long long& pops, unsigned long long& scanned, unsigned long long& fetched) {
     const unsigned FULL = 0xffffffffu;
     const uint8_t bit = (uint8_t)(1 << pass);
     const unsigned lt = (1u << lane) - 1;
@@ -161,6 +161,7 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
             // partial <= pmax for every edge.  (NaN compares false -> falls through.)
             const double pmax = __dmul_rn(base, __ddiv_rn((double)g.wmax[focus], total));
             if (pmax < P.eps) continue;
+            fetched += (unsigned long long)(e - b);  // entries this kernel really reads (scanned counts the reference's)
             for (int64_t k0 = b; k0 < e; k0 += 32) {
                 const int64_t k = k0 + lane;
                 bool take = false;
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
     for (int s = lane; s < hwords; s += 32) hwipe[s] = 0;
     __syncwarp();
 
-    unsigned long long pops = 0, scanned = 0;
+    unsigned long long pops = 0, scanned = 0, fetched = 0;
     float wmaxv = 0.f;
     for (;;) {
         int wi = 0;
@@ -257,13 +258,13 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
             T.insert((uint32_t)bookmark, 0);
         }
         __syncwarp();
-        unsigned long long bp = 0, bs = 0;
+        unsigned long long bp = 0, bs = 0, bf = 0;
         int npop = 0;
-        int n = bca_pass(P, T, 1, 0, lane, npop, bp, bs);
+        int n = bca_pass(P, T, 1, 0, lane, npop, bp, bs, bf);
         if (n > 0 && P.directed) {  // BCAJob.call :32-36 — reverse pass, merged below
             if (lane == 0) { T.key[0] = (uint32_t)bookmark; T.wet[0] = 1.0; }
             __syncwarp();
-            n = bca_pass(P, T, n, 1, lane, npop, bp, bs);
+            n = bca_pass(P, T, n, 1, lane, npop, bp, bs, bf);
         }
         if (n < 0) {  // table overflow: hand the bookmark to the next tier
             if (lane == 0) P.overflow[atomicAdd(P.n_overflow, 1)] = bookmark;
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
             __syncwarp();
             continue;
         }
-        pops += bp; scanned += bs;
+        pops += bp; scanned += bs; fetched += bf;
 
         // ---- BCV.merge (:105-107): fwd + rev per key; then normalise (BookmarkColoring.java:81-91)
         // value of record r:
@@ -330,7 +331,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
                 P.row_cnt[bookmark - P.row_base] = cnt;
             }
         } else {
-            pops -= bp; scanned -= bs;  // will be recounted when the row is re-run
+            pops -= bp; scanned -= bs; fetched -= bf;  // will be recounted when the row is re-run
         }
         for (int s = lane; s < hwords; s += 32) hwipe[s] = 0;  // wipe the index
         __syncwarp();
@@ -338,6 +339,7 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
     if (lane == 0) {
         if (pops) atomicAdd(P.pops, pops);
         if (scanned) atomicAdd(P.scanned, scanned);
+        if (fetched) atomicAdd(P.fetched, fetched);
         if (wmaxv > 0.f) atomicMax(P.gmax_bits, __float_as_int(wmaxv));
     }
 }
@@ -438,7 +440,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     GE_CUDA(cudaMalloc(&row_cnt.p, (size_t)count * 4));
     GE_CUDA(cudaMalloc(&overflow.p, (size_t)count * 4));
     GE_CUDA(cudaMalloc(&deferred.p, (size_t)count * 4));
-    // counters: [0] next, [1] n_overflow, [2] n_deferred, [3] gmax bits, then u64: cursor, pops, scanned
+    // counters: [0] next, [1] n_overflow, [2] n_deferred, [3] gmax bits, then u64: cursor, pops, scanned, fetched
     GE_CUDA(cudaMalloc(&counters.p, 64));
     GE_CUDA(cudaMemsetAsync(counters.p, 0, 64, st));
     GE_CUDA(cudaMemsetAsync(row_start.p, 0xff, (size_t)count * 8, st));
@@ -446,7 +448,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     int32_t* d32 = counters.as<int32_t>();
     unsigned long long* d64 = reinterpret_cast<unsigned long long*>(d32 + 4);
     P.next = d32; P.n_overflow = d32 + 1; P.n_deferred = d32 + 2; P.gmax_bits = d32 + 3;
-    P.cursor = d64; P.pops = d64 + 1; P.scanned = d64 + 2;
+    P.cursor = d64; P.pops = d64 + 1; P.scanned = d64 + 2; P.fetched = d64 + 3;
     P.row_start = row_start.as<int64_t>(); P.row_cnt = row_cnt.as<int32_t>();
     P.overflow = overflow.as<int32_t>(); P.deferred = deferred.as<int32_t>();
 
@@ -554,10 +556,10 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     if (cudaMalloc(&ctx->d_row_off, (size_t)(count + 1) * 8) != cudaSuccess) { cudaGetLastError(); free_arenas(); ctx->err = "out of device memory"; return GE_ERR_NOMEM; }
     scan_counts<<<1, 1024, 0, st>>>(P.row_cnt, count, ctx->d_row_off);
     int64_t nnz = 0;
-    unsigned long long h64[3];
+    unsigned long long h64[4];
     int32_t gbits = 0;
     cudaMemcpyAsync(&nnz, ctx->d_row_off + count, 8, cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(h64, d64, 24, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(h64, d64, 32, cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(&gbits, P.gmax_bits, 4, cudaMemcpyDeviceToHost, st);
     if (cudaStreamSynchronize(st) != cudaSuccess) { free_arenas(); ctx->err = std::string("scan: ") + cudaGetErrorString(cudaGetLastError()); return GE_ERR_CUDA; }
     const size_t nn = (size_t)(nnz > 0 ? nnz : 1);
@@ -573,6 +575,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     ctx->bca_seconds = ms * 1e-3;
     ctx->bca_pops = (int64_t)h64[1];
     ctx->bca_scanned = (int64_t)h64[2];
+    ctx->bca_fetched = (int64_t)h64[3];
     ctx->bca_overflow_rows = overflow_rows;
     ctx->nnz = nnz;
     float gm;

@@ -121,7 +121,7 @@ struct ge_ctx {
     int64_t* d_row_off = nullptr;  // row_count+1 offsets when built here (rows contiguous), else null
     int32_t row_first = 0, row_count = 0;
     int64_t bca_overflow_rows = 0;  // rows that needed the global-memory table tier
-    int64_t bca_pops = 0, bca_scanned = 0;
+    int64_t bca_pops = 0, bca_scanned = 0, bca_fetched = 0;
     double bca_seconds = 0;
 
     // --- embedding store (B1): two arrays of V rows x S floats,
@@ -136,10 +136,9 @@ struct ge_ctx {
     double* d_cost = nullptr;     // epoch cost accumulator
     bool any_hot = false;         // packed nonzeros carry hub damping exponents
     int32_t keep_count = 0x7fffffff;  // ids occurring at least this often are in the L2-resident set
-    // packed array = [cold nonzeros | nonzeros touching an extreme hub]; the second segment has its own launch
-    int64_t n_cold = 0, hub_warps = 0;
-    cudaStream_t hub_stream = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    double hub_kmax = 0;              // hottest id: warps of a full wave expected on it at once
+    int32_t capped_launches = 0;
+    int64_t warp_cap = 0;             // extreme hub present: launches use at most this many warps (ge_warp_cap); 0 = none
     int64_t launch_max_warps = 0, launch_reserve_blocks = 0;  // per-launch overrides (train.cu shape_launch)
     int32_t launch_pf = -1;
     int32_t epoch = 0;
@@ -164,7 +163,9 @@ void ge_free_store(ge_ctx* ctx);
 template <typename T>
 int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
-int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span);  // occurrences from which an id is a hub (damped deltas)
+int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp_cap);
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
+  // occurrences from which an id is a hub (damped deltas)
 void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i, const int32_t* cnt_j, int64_t nj,
                     double div_j, double share_j, int32_t* keep_i, int32_t* keep_j);  // L2-resident set thresholds (raw occurrence counts)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg

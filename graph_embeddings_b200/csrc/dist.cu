@@ -103,6 +103,7 @@ struct DistState {
     uint32_t q = 0;                   // transfers issued per half so far (= sub-epochs done)
     std::vector<cudaEvent_t> xfer_ev; // 2 events per transfer of an epoch (copy alone, no waits)
     std::vector<int32_t> bucket_hot;  // bucket has entries with damping exponents -> HOT kernel variant
+    std::vector<int64_t> bucket_cap;  // warps the bucket's launch may use (train.cu ge_warp_cap); 0 = no cap
     cudaEvent_t c0 = nullptr, c1 = nullptr;
 };
 
@@ -187,6 +188,18 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
         }
         const unsigned long long at = atomicAdd(&cursor[b], 1ULL);
         out[at] = e;
+    }
+}
+
+// largest occurrence count per row block (P = 1) or per half column block (input of ge_warp_cap)
+__global__ void segment_max(const int32_t* __restrict__ cnt, int64_t n, int32_t Bs, int32_t P, int32_t Hs,
+                            int32_t* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const int32_t c = cnt[k];
+        const int blk = (int)(k / Bs);
+        const int seg = blk * P + ((P > 1 && k - (int64_t)blk * Bs >= Hs) ? 1 : 0);
+        if (c > out[seg]) atomicMax(out + seg, c);   // the plain read only filters
     }
 }
 
@@ -402,9 +415,34 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         std::vector<int32_t> hot(2048, 0x7fffffff);   // [0,1024): thresholds, [1024,2048): any-hot flags (out)
         const bool flags = c.update == GE_UPDATE_ATOMIC && c.opt_method == GE_OPT_ADAGRAD;
         for (int b = 0; b < 1024; b++) hot[1024 + b] = 0;
-        for (int b = 0; b < nbuckets; b++) if (flags) hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs);
         r = ge_count_ids(ctx, ctx->d_I, ctx->nnz, first, (int64_t)d->m * d->Bs, &cnt_i);
         if (!r) r = ge_count_ids(ctx, ctx->d_J, ctx->nnz, 0, (int64_t)d->nb * d->Bs, &cnt_j);
+        // per bucket: the launch's warp cap (an extreme hub inside it) and, from the warps it then has,
+        // the occurrence count from which an id is damped
+        d->bucket_cap.assign(nbuckets, 0);
+        ctx->hub_kmax = 0; ctx->capped_launches = 0; ctx->warp_cap = 0;
+        if (!r && flags) {
+            int32_t* d_seg = nullptr;
+            const int nseg_i = d->m, nseg_j = d->nb * d->P;
+            std::vector<int32_t> seg(nseg_i + nseg_j, 0);
+            cudaError_t e = cudaMalloc(&d_seg, seg.size() * 4);
+            if (e == cudaSuccess) e = cudaMemsetAsync(d_seg, 0, seg.size() * 4, st);
+            if (e == cudaSuccess) {
+                segment_max<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_i, (int64_t)d->m * d->Bs, d->Bs, 1, 0, d_seg);
+                segment_max<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_j, (int64_t)d->nb * d->Bs, d->Bs, d->P, d->Hs, d_seg + nseg_i);
+                e = cudaMemcpyAsync(seg.data(), d_seg, seg.size() * 4, cudaMemcpyDeviceToHost, st);
+            }
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            cudaFree(d_seg);
+            if (e != cudaSuccess) { cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_cnt); GE_CUDA(e); }
+            for (int b = 0; b < nbuckets; b++) {
+                const int lrb = b / (d->nb * d->P), cbp = b % (d->nb * d->P);
+                const int64_t mi = seg[lrb] / (d->nb * d->P), mj = seg[nseg_i + cbp] / d->m;   // bucket_scatter's estimates
+                d->bucket_cap[b] = ge_warp_cap(ctx, (int64_t)hc[b], mi > mj ? mi : mj);
+                hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs, d->bucket_cap[b]);
+                if (d->bucket_cap[b] > 0 && (ctx->warp_cap == 0 || d->bucket_cap[b] < ctx->warp_cap)) ctx->warp_cap = d->bucket_cap[b];  // smallest, for ge_train_hub_info
+            }
+        }
         int32_t keep_i = 0x7fffffff, keep_j = 0x7fffffff;
         // one launch = one (row-block, half column-block) bucket: it sees 1/(nb*P) of a row's and 1/m of a
         // column's local nonzeros; 1/m of the rank's flagged W rows and 1/(nb*P) of the flagged C rows are live
@@ -506,9 +544,13 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
                         ctx->err = "cuStreamWaitValue32 (ready flag) failed"; return GE_ERR_CUDA;
                     }
                 }
+                ctx->launch_max_warps = d->bucket_cap[bucket];
+                ctx->launch_pf = d->bucket_cap[bucket] > 0 ? 8 : -1;
                 int r = ge_launch_update(ctx, d->d_nzb + off, cnt, ctx->d_W, Cslot, nullptr,
                                          ekey ^ ((uint64_t)bucket * 0xA24BAED4963EE407ULL), ctx->d_cost, st, d->Bs,
                                          d->bucket_hot[bucket] != 0, piped ? d->d_queue + bucket : nullptr);
+                ctx->launch_max_warps = 0;
+                ctx->launch_pf = -1;
                 if (r) return r;
                 if (k != 0 || (!piped && rot != ROT_CE)) continue;
                 const size_t src_off = (size_t)d->head * slab + part_off[p];

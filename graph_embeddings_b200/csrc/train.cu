@@ -581,7 +581,7 @@ __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __re
                               const float* __restrict__ X, int64_t nnz, int32_t method, int32_t java,
                               double xmax, const int32_t* __restrict__ cnt_i, const int32_t* __restrict__ cnt_j,
                               int32_t hot_count, int32_t keep_i, int32_t keep_j, int32_t* __restrict__ any_hot,
-                              int32_t serial_k, int32_t* __restrict__ any_serial, NzEntry* __restrict__ out) {
+                              NzEntry* __restrict__ out) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
         const float x = X[k];
@@ -597,7 +597,6 @@ __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __re
             if (k) { e.j |= k << GE_ID_BITS; *any_hot = 1; }
             if (c >= keep_j) e.j |= GE_ID_KEEP;
         }
-        if (any_serial && (((e.i >> GE_ID_BITS) & 15) >= serial_k || ((e.j >> GE_ID_BITS) & 15) >= serial_k)) *any_serial = 1;
         if (java) { e.a = x; e.b = 0.f; }
         else if (method == GE_METHOD_GLOVE) {
             e.a = (float)log((double)x);
@@ -610,80 +609,7 @@ __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __re
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// Extreme hubs.  An id whose expected concurrency (ge_damp_bits class k >= serial_k, i.e. more than
-// GE_HUB_SERIAL ~ 64 of the resident warps on one row at once) cannot be repaired by scaling its
-// deltas: measured on a Zipf(1) matrix (5.5 % of all nonzeros on one column) the damped path is
-// 10-30 % off the single-thread loss in the first epoch (profiles/r02_hubs.md).  The reference never
-// has more writers on a row than it has threads.  So the nonzeros touching such an id are moved —
-// stable partition, once, at pack time — into a second segment of the packed array that is processed
-// by its own small launch beside the main one: so few warps that no more than GE_HOT_WRITERS of them
-// sit on the hottest id at once, each walking its share of the segment sequentially with the partner
-// rows prefetched into L2.  The main launch then never touches an extreme hub.
-// ------------------------------------------------------------------------------------------
-constexpr int PART_TILE = 1024;  // entries per block: 256 threads x 4 rounds
-
-__device__ __forceinline__ bool is_serial_entry(const NzEntry& e, int32_t serial_k) {
-    return ((e.i >> GE_ID_BITS) & 15) >= serial_k || ((e.j >> GE_ID_BITS) & 15) >= serial_k;
-}
-
-__global__ void __launch_bounds__(256) partition_count(const NzEntry* __restrict__ nz, int64_t n, int32_t serial_k,
-                                                       uint32_t* __restrict__ tile_hub) {
-    __shared__ uint32_t cnt;
-    if (threadIdx.x == 0) cnt = 0;
-    __syncthreads();
-    const int64_t base = (int64_t)blockIdx.x * PART_TILE;
-    uint32_t mine = 0;
-    for (int r = 0; r < PART_TILE / 256; r++) {
-        const int64_t k = base + r * 256 + threadIdx.x;
-        if (k < n) mine += is_serial_entry(nz[k], serial_k) ? 1u : 0u;
-    }
-    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&cnt, mine);
-    __syncthreads();
-    if (threadIdx.x == 0) tile_hub[blockIdx.x] = cnt;
-}
-
-// stable: cold entries keep their relative order in [0, n_cold), hub entries theirs in [n_cold, n); the
-// concurrency classes that caused the move are cleared (those ids are not damped any more)
-__global__ void __launch_bounds__(256) partition_scatter(const NzEntry* __restrict__ nz, int64_t n, int32_t serial_k,
-                                                         const int64_t* __restrict__ tile_hub_base, int64_t n_cold,
-                                                         NzEntry* __restrict__ out) {
-    __shared__ uint32_t warp_cnt[8];
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int64_t base = (int64_t)blockIdx.x * PART_TILE;
-    const int64_t hub0 = tile_hub_base[blockIdx.x];          // hub entries before this tile
-    const int64_t cold0 = base - hub0;                       // cold entries before this tile
-    for (int r = 0; r < PART_TILE / 256; r++) {
-        const int64_t k = base + r * 256 + threadIdx.x;
-        NzEntry e = {0, 0, 0.f, 0.f};
-        bool hub = false;
-        if (k < n) { e = nz[k]; hub = is_serial_entry(e, serial_k); }
-        const unsigned m = __ballot_sync(0xffffffffu, hub);
-        if (lane == 0) warp_cnt[wid] = __popc(m);
-        __syncthreads();
-        uint32_t before = carry;                             // hub entries of this tile in earlier rounds
-        for (int w = 0; w < wid; w++) before += warp_cnt[w];
-        before += __popc(m & ((1u << lane) - 1));
-        if (k < n) {
-            const int64_t in_tile = (int64_t)r * 256 + threadIdx.x;   // entries of this tile before this one
-            if (hub) {
-                if (((e.i >> GE_ID_BITS) & 15) >= serial_k) e.i &= ~(15 << GE_ID_BITS);
-                if (((e.j >> GE_ID_BITS) & 15) >= serial_k) e.j &= ~(15 << GE_ID_BITS);
-                out[n_cold + hub0 + before] = e;
-            } else {
-                out[cold0 + (in_tile - before)] = e;
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < 8; w++) t += warp_cnt[w]; carry += t; }
-        __syncthreads();
-    }
-}
-
+// largest occurrence count of any id (input of the concurrency cap, ge_warp_cap)
 __global__ void max_count(const int32_t* __restrict__ cnt, int64_t n, int32_t* __restrict__ out) {
     int32_t m = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -899,7 +825,7 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
 }
 
 void ge_free_store(ge_ctx* ctx) {
-    ctx->n_cold = 0; ctx->hub_warps = 0;
+    ctx->warp_cap = 0;
     cudaFree(ctx->d_W); cudaFree(ctx->d_C); cudaFree(ctx->d_nz); cudaFree(ctx->d_perm); cudaFree(ctx->d_cost);
     ctx->d_W = ctx->d_C = nullptr; ctx->d_nz = nullptr; ctx->d_perm = nullptr; ctx->d_cost = nullptr;
     ctx->have_store = false;
@@ -1028,14 +954,49 @@ int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, i
 // (Adagrad.java:76-80).  Hot ids get a damping exponent (common.cuh ge_damp_bits) that scales their
 // deltas so the sum stays below GE_HOT_WRITERS full steps.  Returns the occurrence count from which
 // an id is hot.
-int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span) {
+int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp_cap) {
     const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
     double warps = (double)ctx->sm_count * 32.0;        // 4 blocks x 8 warps per SM at most
     if (warps > (double)span / 16.0) warps = (double)span / 16.0;   // wave_grid's cap for tiny problems
+    if (warp_cap > 0 && warps > (double)warp_cap) warps = (double)warp_cap;
     if (warps < 1) warps = 1;
     double c = writers * (double)launch_nnz / warps;
     if (c < 1) c = 1;
     return c > 2e9 ? 0x7fffffff : (int32_t)c;
+}
+
+// Extreme hubs.  Scaling a hub's deltas (above) is accurate while a few dozen warps share the row —
+// every BCA-built matrix of the BASELINE configs — but not when one id holds percents of all
+// nonzeros: on a Zipf(1) matrix (5.5 % on one column, ~1 000 concurrent warps) the damped path is
+// 10-30 % off the single-thread loss in the first epoch, and moving such nonzeros into a launch of
+// their own changes the visiting order and with it the online loss (profiles/r02_hubs.md).  The
+// reference never has more writers on a row than threads.  So the launch itself is capped: when the
+// hottest id would have GE_HUB_ONSET (default 64) or more of a full wave's warps on it at once, the
+// launch gets only as many warps as put GE_HUB_SERIAL (default 16 = GE_HOT_WRITERS: nothing is left to
+// damp) on it; the uniform shuffled order is kept.  The epoch then runs at the hub's own pace
+// (count x per-nonzero latency / 16), which is what bounded staleness on that row costs.
+// GE_HUB_SERIAL=0 switches the cap off.  Returns 0 = no cap.
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count) {
+    const double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 16.0;
+    const double onset = getenv("GE_HUB_ONSET") ? atof(getenv("GE_HUB_ONSET")) : 64.0;
+    if (max_count <= 0 || launch_nnz <= 0) return 0;
+    const double full = (double)ctx->sm_count * 32.0;
+    const double k = full * (double)max_count / (double)launch_nnz;   // warps of a full wave on the hottest id
+    if (k > ctx->hub_kmax) ctx->hub_kmax = k;
+    if (serial <= 0 || k < onset || k <= serial) return 0;
+    const double w = serial * (double)launch_nnz / (double)max_count;
+    ctx->capped_launches++;
+    return w < 1 ? 1 : (int64_t)w;
+}
+
+// hottest id over all launches shaped since the last prepare: expected concurrent warps on it in an
+// uncapped wave, and how many launches (1 for the single-GPU trainer, buckets for the block schedule) are capped
+extern "C" int ge_train_hub_info(ge_ctx* ctx, double* max_concurrency, int32_t* capped_launches, int64_t* warp_cap) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (max_concurrency) *max_concurrency = ctx->hub_kmax;
+    if (capped_launches) *capped_launches = ctx->capped_launches;
+    if (warp_cap) *warp_cap = ctx->warp_cap;
+    return GE_OK;
 }
 
 int ge_train_prepare(ge_ctx* ctx) {
@@ -1054,70 +1015,32 @@ int ge_train_prepare(ge_ctx* ctx) {
         int32_t keep_i, keep_j;
         ge_keep_counts(ctx, cnt_i, ctx->V, 1.0, 1.0, cnt_j, ctx->V, 1.0, 1.0, &keep_i, &keep_j);
         ctx->keep_count = keep_i;
-        // extreme hubs (more than GE_HUB_SERIAL ~ 64 expected concurrent warps; 0 = never) get their own
-        // bounded-concurrency segment — device epoch order only: GE_ORDER_JAVA is the reference's order
-        // over the COO positions and cannot be re-partitioned
-        const int32_t hot = ge_hot_count(ctx, ctx->nnz, ctx->V);
-        const double hub_serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 64.0;
-        const double hot_writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
-        int32_t serial_k = 16;  // class from which an id is "extreme": K ~ hot_writers * 2^((k - 0.5) / 2) >= hub_serial
-        if (cnt_i && hub_serial > 0 && c.order == GE_ORDER_DEVICE && !c.serial) {
-            serial_k = (int32_t)ceil(2.0 * log2(hub_serial / hot_writers) + 0.5);
-            if (serial_k < 1) serial_k = 1;
+        int32_t* d_flags = nullptr;   // [0] any damped id, [1] max occurrence count
+        GE_CUDA(cudaMalloc(&d_flags, 8));
+        cudaMemsetAsync(d_flags, 0, 8, ctx->stream);
+        int32_t fl[2] = {0, 0};
+        cudaError_t pe = cudaSuccess;
+        ctx->warp_cap = 0;
+        ctx->hub_kmax = 0; ctx->capped_launches = 0;
+        if (cnt_i) {
+            max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_i, ctx->V, d_flags + 1);
+            max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, ctx->V, d_flags + 1);
+            pe = cudaMemcpyAsync(fl, d_flags, 8, cudaMemcpyDeviceToHost, ctx->stream);
+            if (pe == cudaSuccess) pe = cudaStreamSynchronize(ctx->stream);
+            if (pe == cudaSuccess) ctx->warp_cap = ge_warp_cap(ctx, ctx->nnz, fl[1]);
         }
-        int32_t* d_flags = nullptr;   // [0] any damped id, [1] any extreme id, [2] max occurrence count
-        GE_CUDA(cudaMalloc(&d_flags, 16));
-        cudaMemsetAsync(d_flags, 0, 16, ctx->stream);
-        pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
-                                                                 c.math == GE_MATH_JAVA, ctx->xmax, cnt_i, cnt_j, hot, keep_i, keep_j,
-                                                                 d_flags, serial_k, serial_k <= 15 ? d_flags + 1 : nullptr, ctx->d_nz);
-        if (cnt_i && serial_k <= 15) {
-            max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_i, ctx->V, d_flags + 2);
-            max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, ctx->V, d_flags + 2);
+        if (pe == cudaSuccess) {
+            pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
+                                                                     c.math == GE_MATH_JAVA, ctx->xmax, cnt_i, cnt_j,
+                                                                     ge_hot_count(ctx, ctx->nnz, ctx->V, ctx->warp_cap), keep_i, keep_j,
+                                                                     d_flags, ctx->d_nz);
+            pe = cudaGetLastError();
         }
-        cudaError_t pe = cudaGetLastError();
-        int32_t fl[3] = {0, 0, 0};
-        if (pe == cudaSuccess) pe = cudaMemcpyAsync(fl, d_flags, 12, cudaMemcpyDeviceToHost, ctx->stream);
+        if (pe == cudaSuccess) pe = cudaMemcpyAsync(fl, d_flags, 4, cudaMemcpyDeviceToHost, ctx->stream);
         if (pe == cudaSuccess) pe = cudaStreamSynchronize(ctx->stream);
         cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_flags);
         GE_CUDA(pe);
         ctx->any_hot = fl[0] != 0;
-        ctx->n_cold = ctx->nnz;
-        ctx->hub_warps = 0;
-        if (fl[1]) {
-            // ---- stable partition: [cold | nonzeros touching an extreme hub]
-            const int64_t tiles = (ctx->nnz + PART_TILE - 1) / PART_TILE;
-            uint32_t* d_tile = nullptr;
-            int64_t* d_base = nullptr;
-            NzEntry* d_out = nullptr;
-            std::vector<uint32_t> h_tile(tiles);
-            std::vector<int64_t> h_base(tiles);
-            cudaError_t e = cudaMalloc(&d_tile, (size_t)tiles * 4);
-            if (e == cudaSuccess) e = cudaMalloc(&d_base, (size_t)tiles * 8);
-            if (e == cudaSuccess) e = cudaMalloc(&d_out, (size_t)ctx->nnz * sizeof(NzEntry));
-            if (e == cudaSuccess) {
-                partition_count<<<(unsigned)tiles, 256, 0, ctx->stream>>>(ctx->d_nz, ctx->nnz, serial_k, d_tile);
-                e = cudaMemcpyAsync(h_tile.data(), d_tile, (size_t)tiles * 4, cudaMemcpyDeviceToHost, ctx->stream);
-            }
-            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-            int64_t n_hub = 0;
-            for (int64_t t = 0; t < tiles && e == cudaSuccess; t++) { h_base[t] = n_hub; n_hub += h_tile[t]; }
-            if (e == cudaSuccess) e = cudaMemcpyAsync(d_base, h_base.data(), (size_t)tiles * 8, cudaMemcpyHostToDevice, ctx->stream);
-            if (e == cudaSuccess) {
-                partition_scatter<<<(unsigned)tiles, 256, 0, ctx->stream>>>(ctx->d_nz, ctx->nnz, serial_k, d_base, ctx->nnz - n_hub, d_out);
-                e = cudaGetLastError();
-            }
-            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-            cudaFree(d_tile); cudaFree(d_base);
-            if (e != cudaSuccess) { cudaFree(d_out); GE_CUDA(e); }
-            cudaFree(ctx->d_nz);
-            ctx->d_nz = d_out;
-            ctx->n_cold = ctx->nnz - n_hub;
-            // so few warps that at most GE_HOT_WRITERS of them sit on the hottest id (all of whose fl[2]
-            // occurrences are in this segment) at once
-            double w = hot_writers * (double)n_hub / (double)(fl[2] > 0 ? fl[2] : 1);
-            ctx->hub_warps = w < 1 ? 1 : (w > 1e9 ? 1000000000 : (int64_t)w);
-        }
     }
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
     if (c.order == GE_ORDER_JAVA) {
@@ -1150,32 +1073,13 @@ extern "C" int ge_train_epoch(ge_ctx* ctx, double* cost) {
     }
     GE_CUDA(cudaMemsetAsync(ctx->d_cost, 0, sizeof(double), ctx->stream));
     GE_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-    const int64_t n_hub = perm ? 0 : ctx->nnz - ctx->n_cold;
-    if (n_hub > 0) {
-        // extreme-hub segment: its own small launch on a second stream, started first so that its few
-        // blocks are resident beside the main launch (whose wave is shrunk by as many blocks)
-        if (!ctx->hub_stream) {
-            GE_CUDA(cudaStreamCreateWithFlags(&ctx->hub_stream, cudaStreamNonBlocking));
-            GE_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-            GE_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-        }
-        GE_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream));
-        GE_CUDA(cudaStreamWaitEvent(ctx->hub_stream, ctx->ev_fork, 0));
-        ctx->launch_max_warps = ctx->hub_warps;
-        ctx->launch_pf = 8;   // partner rows of the nonzero 8 steps ahead are pulled into L2
-        r = ge_launch_update(ctx, ctx->d_nz + ctx->n_cold, n_hub, ctx->d_W, ctx->d_C, nullptr,
-                             epoch_key(c.seed, ctx->epoch) ^ 0x5851F42D4C957F2DULL, ctx->d_cost, ctx->hub_stream, ctx->V, ctx->any_hot, nullptr);
-        ctx->launch_max_warps = 0;
-        ctx->launch_pf = -1;
-        if (r) return r;
-        GE_CUDA(cudaEventRecord(ctx->ev_join, ctx->hub_stream));
-        ctx->launch_reserve_blocks = (ctx->hub_warps + 7) / 8;
-    }
-    r = ge_launch_update(ctx, ctx->d_nz, perm ? ctx->nnz : ctx->n_cold, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
+    ctx->launch_max_warps = ctx->warp_cap;           // 0 = none; see ge_warp_cap
+    ctx->launch_pf = ctx->warp_cap > 0 ? 8 : -1;     // few warps are latency-bound: pull the rows 8 nonzeros ahead into L2
+    r = ge_launch_update(ctx, ctx->d_nz, ctx->nnz, ctx->d_W, ctx->d_C, perm, epoch_key(c.seed, ctx->epoch),
                          ctx->d_cost, ctx->stream, ctx->V, ctx->any_hot, nullptr);
-    ctx->launch_reserve_blocks = 0;
+    ctx->launch_max_warps = 0;
+    ctx->launch_pf = -1;
     if (r) return r;
-    if (n_hub > 0) GE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     GE_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
     double total = 0;
     GE_CUDA(cudaMemcpyAsync(&total, ctx->d_cost, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1361,14 +1265,7 @@ extern "C" int ge_epoch_order(ge_ctx* ctx, int32_t epoch, int32_t* perm, int64_t
     }
     int32_t* d = nullptr;
     GE_CUDA(cudaMalloc(&d, (size_t)ctx->nnz * sizeof(int32_t)));
-    // positions in the PACKED array ([cold | extreme-hub segment], each walked under its own bijection)
-    int r0 = ge_train_prepare(ctx);
-    if (r0) { cudaFree(d); return r0; }
-    const int64_t n_cold = ctx->n_cold, n_hub = ctx->nnz - n_cold;
-    if (n_cold > 0)
-        materialise_order<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(Bijection::make((uint64_t)n_cold, epoch_key(ctx->cfg.seed, epoch)), n_cold, d, 0);
-    if (n_hub > 0)
-        materialise_order<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(Bijection::make((uint64_t)n_hub, epoch_key(ctx->cfg.seed, epoch) ^ 0x5851F42D4C957F2DULL), n_hub, d + n_cold, (int32_t)n_cold);
+    materialise_order<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(Bijection::make((uint64_t)ctx->nnz, epoch_key(ctx->cfg.seed, epoch)), ctx->nnz, d, 0);
     cudaError_t e = cudaMemcpyAsync(perm, d, (size_t)ctx->nnz * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(d);

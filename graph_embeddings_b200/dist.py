@@ -64,7 +64,9 @@ class DistTrainer:
     def cooc_stats(self):
         pops, scanned, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
         self._n.ck(self._n.L.ge_cooc_stats(self._n.h, C.byref(pops), C.byref(scanned), C.byref(sec)))
-        return {"pops": pops.value, "scanned": scanned.value, "seconds": sec.value}
+        fetched = C.c_int64(0)
+        self._n.ck(self._n.L.ge_cooc_fetched(self._n.h, C.byref(fetched)))
+        return {"pops": pops.value, "scanned": scanned.value, "fetched": fetched.value, "seconds": sec.value}
 
     def prepare(self):
         self._n.ck(self._n.L.ge_dist_prepare(self._n.h, self.nb))
@@ -95,8 +97,11 @@ class DistTrainer:
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
         rot = {-1: "pointer shift (1 GPU)", 0: "nccl send/recv in-stream", 1: "nccl half blocks, second stream",
                2: "copy engine into the neighbour's IPC-mapped ring"}.get(self._n.L.ge_dist_rotation_mode(self._n.h), "?")
+        k, nc, w = C.c_double(0), C.c_int32(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(nc), C.byref(w)))
         return {"bucket_nnz": b[:n].copy(), "comm_seconds": comm.value, "nnz_global": nnzg.value, "rotation": rot,
-                "update_seconds": s.value, "launches": l.value, "updates": u.value}
+                "update_seconds": s.value, "launches": l.value, "updates": u.value,
+                "hub": {"max_concurrency": k.value, "capped_launches": nc.value, "warp_cap": w.value}}
 
     def set_stream(self, s):
         self._n.set_stream(s)

@@ -197,6 +197,9 @@ int ge_cooc_build(ge_ctx*, int64_t* nnz, double* xmax);
 int ge_cooc_build_rows(ge_ctx*, int32_t first, int32_t count, int64_t* nnz, double* xmax);
 /* counters of the last build: pops (pair events), scanned adjacency entries, seconds on device */
 int ge_cooc_stats(ge_ctx*, int64_t* pops, int64_t* scanned, double* seconds);
+/* adjacency entries the last build really read: `scanned` counts every entry the reference's loop visits
+ * (DirectedWeighted.java:79-98); lists whose heaviest edge cannot reach epsilon are skipped unread here */
+int ge_cooc_fetched(ge_ctx*, int64_t* fetched);
 
 /* A6 — cIdx_I/J/C for all k (unpermuted); cap = capacity of the three arrays. */
 int ge_cooc_export(ge_ctx*, int32_t* I, int32_t* J, float* X, int64_t cap);
@@ -229,6 +232,14 @@ int ge_epoch_order(ge_ctx*, int32_t epoch, int32_t* perm, int64_t cap);
 int ge_train_reset(ge_ctx*);
 /* device seconds and kernel launches spent in update kernels so far */
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
+/* Hub report of the prepared trainer (single-GPU or block schedule).  The reference has at most
+ * nproc-1 writers on an embedding row (Optimizer.java:84-92); a GPU wave has 18 944 warps.  Ids that
+ * would see more than GE_HOT_WRITERS (16) of them get damped deltas; when the hottest id would see
+ * GE_HUB_ONSET (64) or more, the launch is capped to the warp count that puts GE_HUB_SERIAL (16) on it.
+ *   max_concurrency : warps of an uncapped wave expected on the hottest id at once
+ *   capped_launches : launches (1, or buckets of the block schedule) that run capped
+ *   warp_cap        : the (smallest) cap, 0 = none */
+int ge_train_hub_info(ge_ctx*, double* max_concurrency, int32_t* capped_launches, int64_t* warp_cap);
 
 /* SURVEY §8(f) row 2 — EmbeddingTextWriter.write (J/util/write/EmbeddingTextWriter.java:73-149)
  * served from the device store: <vectors_path> gets one line of "%11.6E" values (Java Formatter

@@ -87,15 +87,42 @@ def zipf():
         out[upd] = [opt.epoch() for _ in range(epochs)]
         out[upd + "_ms"] = opt.stats()["update_seconds"] / epochs * 1e3
     c = Configuration(method="glove", dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=31)
+    opt = createOptimizer(c, ImportedMatrix(V, I, J, X, c, xmax=0.2))
+    out["hub"] = opt.stats()["hub"]
+    del opt
     tr = DistTrainer(c, 0, 1, 8, None)
     tr.import_rows(V, I, J, X, xmax=0.2)
     tr.prepare()
     out["dist8x8"] = [tr.epoch() for _ in range(epochs)]
+    out["dist_hub"] = tr.stats()["hub"]
+    out["dist8x8_ms"] = tr.stats()["update_seconds"] / epochs * 1e3
+    # the oracle walking the same block order (sub-epoch s: half blocks (k, (k+s) mod 8, p), random inside)
+    Bs = (V + 7) // 8
+    Hs = (Bs + 1) // 2
+    bucket = ((I // Bs) * 8 + J // Bs) * 2 + (J % Bs >= Hs)
+    srt = np.argsort(bucket, kind="stable")
+    start = np.searchsorted(bucket[srt], np.arange(129))
+    rng = np.random.default_rng(1)
+    t = oracle.Trainer(V, I, J, X, 0.2, dim, "glove", 31)
+    for _ in range(epochs):
+        order = []
+        for s_ in range(8):
+            for k in range(8):
+                for p_ in range(2):
+                    b = (k * 8 + (k + s_) % 8) * 2 + p_
+                    order.append(rng.permutation(srt[start[b]:start[b + 1]]))
+        t.set_perm(np.concatenate(order).astype(np.int32))
+        t.epoch(False)
+    out["oracle_blockwalk"] = t.history_exact().tolist()
+    t.close()
     o = np.array(out["oracle"])
     for k in ("atomic", "store", "dist8x8"):
         out[k + "_rel"] = (np.abs(np.array(out[k]) - o) / o).tolist()
+    ob = np.array(out["oracle_blockwalk"])
+    out["dist8x8_rel_blockwalk"] = (np.abs(np.array(out["dist8x8"]) - ob) / ob).tolist()
     print(json.dumps(out), flush=True)
-    with open(os.path.join(OUT, f"probe_zipf_w{out['hot_writers']}.json"), "w") as f:
+    tag = "w%s_hs%s_on%s" % (out["hot_writers"], os.environ.get("GE_HUB_SERIAL", "16"), os.environ.get("GE_HUB_ONSET", "64"))
+    with open(os.path.join(OUT, f"probe_zipf_{tag}.json"), "w") as f:
         json.dump(out, f)
 
 
