@@ -426,7 +426,7 @@ def run_single(args):
                        "method": "glove", "optimizer": "adagrad", "math": "f32 fast path, atomic red.add row updates",
                        "l2": "inputs larger than L2 (store %.1f GB + nonzeros %.1f GB)" % (
                            2 * g.V * ((2 * dim + 9) // 8 * 8) * 4 / 1e9, nnz * 16 / 1e9),
-                       "final_cost": costs[-1]},
+                       "hub": s1["hub"], "final_cost": costs[-1]},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "glove_adagrad_update", "bytes_per_nnz": B,
                          "peak_source": peak_src, "kernel_ms": kern_s * 1e3},

@@ -164,7 +164,7 @@ template <typename T>
 int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp_cap);
-int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, bool block_schedule);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
   // occurrences from which an id is a hub (damped deltas)
 void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i, const int32_t* cnt_j, int64_t nj,
                     double div_j, double share_j, int32_t* keep_i, int32_t* keep_j);  // L2-resident set thresholds (raw occurrence counts)

@@ -438,7 +438,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
             for (int b = 0; b < nbuckets; b++) {
                 const int lrb = b / (d->nb * d->P), cbp = b % (d->nb * d->P);
                 const int64_t mi = seg[lrb] / (d->nb * d->P), mj = seg[nseg_i + cbp] / d->m;   // bucket_scatter's estimates
-                d->bucket_cap[b] = ge_warp_cap(ctx, (int64_t)hc[b], mi > mj ? mi : mj);
+                d->bucket_cap[b] = ge_warp_cap(ctx, (int64_t)hc[b], mi > mj ? mi : mj, true);
                 hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs, d->bucket_cap[b]);
                 if (d->bucket_cap[b] > 0 && (ctx->warp_cap == 0 || d->bucket_cap[b] < ctx->warp_cap)) ctx->warp_cap = d->bucket_cap[b];  // smallest, for ge_train_hub_info
             }

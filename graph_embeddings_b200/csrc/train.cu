@@ -825,7 +825,6 @@ int ge_launch_update(ge_ctx* ctx, const NzEntry* nz, int64_t count, float* W, fl
 }
 
 void ge_free_store(ge_ctx* ctx) {
-    ctx->warp_cap = 0;
     cudaFree(ctx->d_W); cudaFree(ctx->d_C); cudaFree(ctx->d_nz); cudaFree(ctx->d_perm); cudaFree(ctx->d_cost);
     ctx->d_W = ctx->d_C = nullptr; ctx->d_nz = nullptr; ctx->d_perm = nullptr; ctx->d_cost = nullptr;
     ctx->have_store = false;
@@ -967,18 +966,26 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 
 // Extreme hubs.  Scaling a hub's deltas (above) is accurate while a few dozen warps share the row —
 // every BCA-built matrix of the BASELINE configs — but not when one id holds percents of all
-// nonzeros: on a Zipf(1) matrix (5.5 % on one column, ~1 000 concurrent warps) the damped path is
+// nonzeros: on a Zipf(1) matrix (5.5 % on one column, ~260 of the 4 736 resident warps on it) the damped path is
 // 10-30 % off the single-thread loss in the first epoch, and moving such nonzeros into a launch of
 // their own changes the visiting order and with it the online loss (profiles/r02_hubs.md).  The
 // reference never has more writers on a row than threads.  So the launch itself is capped: when the
 // hottest id would have GE_HUB_ONSET (default 64) or more of a full wave's warps on it at once, the
-// launch gets only as many warps as put GE_HUB_SERIAL (default 16 = GE_HOT_WRITERS: nothing is left to
-// damp) on it; the uniform shuffled order is kept.  The epoch then runs at the hub's own pace
-// (count x per-nonzero latency / 16), which is what bounded staleness on that row costs.
+// launch gets only as many warps as put GE_HUB_SERIAL (default 8) on it; the uniform shuffled order is
+// kept.  Measured vs the single-thread oracle on that matrix, first epoch / later epochs: 16 on the hub
+// 2.0 % / <= 0.6 %, 8 on the hub 0.23 % / <= 0.13 %.  Inside the block schedule's buckets, where the hub
+// is 12-50 % of a launch instead of 5 %, the same count is far less accurate (16: 38 %, 8: 2.0 % /
+// <= 0.4 %), so the buckets use half of it (4: 0.45 % / <= 0.14 % against the oracle walking the block
+// order) and, being 16x more concentrated for any matrix, engage from 4x the onset.  The epoch then runs at the hub's own pace
+// (count x per-nonzero latency / writers), which is what bounded staleness on that row costs.
 // GE_HUB_SERIAL=0 switches the cap off.  Returns 0 = no cap.
-int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count) {
-    const double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 16.0;
-    const double onset = getenv("GE_HUB_ONSET") ? atof(getenv("GE_HUB_ONSET")) : 64.0;
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, bool block_schedule) {
+    double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 8.0;
+    if (block_schedule) serial = getenv("GE_HUB_SERIAL_BLOCKS") ? atof(getenv("GE_HUB_SERIAL_BLOCKS")) : 0.5 * serial;
+    // buckets concentrate a column's nonzeros 16x (8 GPUs x 2 halves): C4's hottest column sits at ~85 of a
+    // full wave's warps inside its buckets, damped and checked against the 1-rank walk; Zipf(1) at 2 343
+    double onset = getenv("GE_HUB_ONSET") ? atof(getenv("GE_HUB_ONSET")) : 64.0;
+    if (block_schedule) onset = getenv("GE_HUB_ONSET_BLOCKS") ? atof(getenv("GE_HUB_ONSET_BLOCKS")) : 4.0 * onset;
     if (max_count <= 0 || launch_nnz <= 0) return 0;
     const double full = (double)ctx->sm_count * 32.0;
     const double k = full * (double)max_count / (double)launch_nnz;   // warps of a full wave on the hottest id
@@ -1027,7 +1034,7 @@ int ge_train_prepare(ge_ctx* ctx) {
             max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, ctx->V, d_flags + 1);
             pe = cudaMemcpyAsync(fl, d_flags, 8, cudaMemcpyDeviceToHost, ctx->stream);
             if (pe == cudaSuccess) pe = cudaStreamSynchronize(ctx->stream);
-            if (pe == cudaSuccess) ctx->warp_cap = ge_warp_cap(ctx, ctx->nnz, fl[1]);
+            if (pe == cudaSuccess) ctx->warp_cap = ge_warp_cap(ctx, ctx->nnz, fl[1], false);
         }
         if (pe == cudaSuccess) {
             pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,

@@ -135,6 +135,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
                            "l2": "inputs larger than L2", "final_cost": costs[-1],
                            "nnz_per_rank": [int(x) for x in A[:, 5]],
                            "rotation_copy_seconds_per_epoch_max": float(A[:, 4].max() / K),
+                           "hub": tr.stats()["hub"],
                            "check_vs_1rank": check},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
                              "frac": achieved / (peak * world), "traffic": None, "kernel": "glove_adagrad_update",

@@ -233,9 +233,10 @@ int ge_train_reset(ge_ctx*);
 /* device seconds and kernel launches spent in update kernels so far */
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
 /* Hub report of the prepared trainer (single-GPU or block schedule).  The reference has at most
- * nproc-1 writers on an embedding row (Optimizer.java:84-92); a GPU wave has 18 944 warps.  Ids that
+ * nproc-1 writers on an embedding row (Optimizer.java:84-92); a GPU wave has 4 736 warps.  Ids that
  * would see more than GE_HOT_WRITERS (16) of them get damped deltas; when the hottest id would see
- * GE_HUB_ONSET (64) or more, the launch is capped to the warp count that puts GE_HUB_SERIAL (16) on it.
+ * GE_HUB_ONSET (64) or more, the launch is capped to the warp count that puts GE_HUB_SERIAL (8; half of
+ * it in the buckets of the block schedule) on it.
  *   max_concurrency : warps of an uncapped wave expected on the hottest id at once
  *   capped_launches : launches (1, or buckets of the block schedule) that run capped
  *   warp_cap        : the (smallest) cap, 0 = none */

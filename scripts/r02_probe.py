@@ -88,6 +88,7 @@ def zipf():
         out[upd + "_ms"] = opt.stats()["update_seconds"] / epochs * 1e3
     c = Configuration(method="glove", dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=31)
     opt = createOptimizer(c, ImportedMatrix(V, I, J, X, c, xmax=0.2))
+    opt.epoch()
     out["hub"] = opt.stats()["hub"]
     del opt
     tr = DistTrainer(c, 0, 1, 8, None)
