@@ -371,12 +371,15 @@ def run_single(args):
     t0 = time.time()
     bca = BookmarkColoring(g, cfg)
     opt = createOptimizer(cfg, bca)
+    torch.cuda.synchronize()
     t_build = time.time() - t0
     for _ in range(K):
         opt.epoch()                                  # each returns the epoch loss (8 B D2H)
+    t_epochs = time.time() - t0 - t_build
     emb = opt.extractResult()                        # what the seam returns: double[V * dim] (Optimizer.java:130-140)
     torch.cuda.synchronize()
     t_e2e = time.time() - t0
+    phases = {"handoff+build+init": round(t_build, 3), "epochs": round(t_epochs, 3), "extract": round(t_e2e - t_build - t_epochs, 3)}
     nnz = bca.coOccurrenceCount()
     cst = bca.stats()
     h2d = g.out_off.nbytes * 2 + g.out_nbr.nbytes * 2 + g.out_w.nbytes * 2
@@ -437,7 +440,7 @@ def run_single(args):
                      "note": "scanned_reference = adjacency entries the reference's loop visits; fetched = entries "
                              "this kernel reads (hub lists that provably cannot reach epsilon are skipped)"},
             "e2e": {"value": nnz * K / t_e2e, "unit": "nnz_updates/s", "h2d_bytes_per_step": h2d / K,
-                    "d2h_bytes_per_step": d2h / K, "seconds": t_e2e,
+                    "d2h_bytes_per_step": d2h / K, "seconds": t_e2e, "phases": phases,
                     "includes": "graph hand-off H2D, BCA build, store init, K epochs with loss read-back, "
                                 "f64 result (f32 over PCIe, widened on the host)"},
             "gpu_launches": int(s1["launches"] - s0["launches"]), "clocks": clk}

@@ -337,10 +337,10 @@ class Adagrad(IOptimizer):
     def stats(self):
         s, l, u = C.c_double(0), C.c_int64(0), C.c_int64(0)
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
-        k, n, w = C.c_double(0), C.c_int32(0), C.c_int64(0)
-        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(n), C.byref(w)))
+        k, sh, n, w = C.c_double(0), C.c_double(0), C.c_int32(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(sh), C.byref(n), C.byref(w)))
         return {"update_seconds": s.value, "launches": l.value, "updates": u.value,
-                "hub": {"max_concurrency": k.value, "capped_launches": n.value, "warp_cap": w.value}}
+                "hub": {"max_concurrency": k.value, "damped_share": sh.value, "capped_launches": n.value, "warp_cap": w.value}}
 
     def reset(self):
         """A fresh optimizer on the same matrix (new Adagrad(coMatrix, ...), Main.java:72): store

@@ -326,6 +326,25 @@ extern "C" int ge_cooc_build_rows(ge_ctx* ctx, int32_t first, int32_t count, int
 }
 extern "C" int ge_cooc_build(ge_ctx* ctx, int64_t* nnz, double* xmax) { return ge_cooc_build_rows(ctx, 0, -1, nnz, xmax); }
 
+// rows of a cyclic block layout (common.cuh ge_vid): the `count` virtual ids from `first_vid` on, i.e. whole
+// blocks {b, b + nblocks, ...}; the COO comes out in virtual-id order with the real ids in I and J
+extern "C" int ge_cooc_build_rows_cyclic(ge_ctx* ctx, int32_t nblocks, int32_t first_vid, int32_t count, int64_t* nnz, double* xmax) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (!ctx->d_out_off) { ctx->err = "no graph: call ge_set_graph_csr first"; return GE_ERR_STATE; }
+    cudaSetDevice(ctx->cfg.device);
+    if (nblocks < 1 || nblocks > 32) { ctx->err = "nblocks out of range"; return GE_ERR_INVALID; }
+    const int32_t Bs = (ctx->V + nblocks - 1) / nblocks;
+    if (first_vid < 0 || count < 0 || first_vid % Bs || count % Bs || first_vid + (int64_t)count > (int64_t)nblocks * Bs) {
+        ctx->err = "cyclic row range must be whole blocks"; return GE_ERR_INVALID;
+    }
+    ge_free_cooc(ctx);
+    int r = ge_bca_build(ctx, first_vid, count, nblocks, Bs);
+    if (r) return r;
+    if (nnz) *nnz = ctx->nnz;
+    if (xmax) *xmax = ctx->xmax;
+    return GE_OK;
+}
+
 extern "C" int ge_cooc_stats(ge_ctx* ctx, int64_t* pops, int64_t* scanned, double* seconds) {
     if (!ctx) return GE_ERR_INVALID;
     if (pops) *pops = ctx->bca_pops;

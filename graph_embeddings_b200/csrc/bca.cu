@@ -43,6 +43,7 @@ struct BcaParams {
     // work: bookmarks work[0..nwork) or, when work == nullptr, first .. first+nwork
     const int32_t* work;
     int32_t nwork, first, row_base;  // row_base: index 0 of row_start/row_cnt
+    int32_t lay_nb, lay_Bs;          // cyclic block layout: first / row_base are virtual ids (common.cuh ge_vid)
     int32_t* next;                   // dynamic work counter
     // table geometry
     int32_t cap, hcap_log2;
@@ -250,7 +251,9 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         if (lane == 0) wi = atomicAdd(P.next, 1);
         wi = __shfl_sync(FULL, wi, 0);
         if (wi >= P.nwork) break;
-        const int32_t bookmark = P.work ? P.work[wi] : P.first + wi;
+        const int32_t bookmark = P.work ? P.work[wi] : ge_vid_inv(P.first + wi, P.lay_nb, P.lay_Bs);
+        if (bookmark >= P.V) continue;  // padding slot of a cyclic block
+        const int32_t slot = ge_vid(bookmark, P.lay_nb, P.lay_Bs) - P.row_base;
 
         // nodeTree.put(bookmark, new PaintedNode(bookmark, 1)) (:39)
         if (lane == 0) {
@@ -327,8 +330,8 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         if (start >= 0) {
             wmaxv = fmaxf(wmaxv, rmax);
             if (lane == 0) {
-                P.row_start[bookmark - P.row_base] = P.arena_base + start;
-                P.row_cnt[bookmark - P.row_base] = cnt;
+                P.row_start[slot] = P.arena_base + start;
+                P.row_cnt[slot] = cnt;
             }
         } else {
             pops -= bp; scanned -= bs; fetched -= bf;  // will be recounted when the row is re-run
@@ -419,7 +422,7 @@ struct DevBuf {  // frees on scope exit
 };
 }  // namespace
 
-int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
+int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int32_t lay_Bs) {
     const ge_config& c = ctx->cfg;
     cudaStream_t st = ctx->stream;
     BcaParams P{};
@@ -429,6 +432,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     P.alpha = c.alpha; P.eps = c.epsilon; P.one_minus_alpha = 1 - c.alpha;  // Java: (1 - alpha), fp64
     P.directed = c.directed; P.normalize = c.normalize;
     P.first = first; P.row_base = first;
+    P.lay_nb = lay_nb; P.lay_Bs = lay_Bs;
 
     // bound on records per bookmark: every pop but the root retires >= alpha*eps paint per pass
     double bound = 2.0 / (c.alpha * c.epsilon) + 2.0;
@@ -581,7 +585,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count) {
     float gm;
     memcpy(&gm, &gbits, 4);
     ctx->xmax = (double)gm;  // BookmarkColoring.max starts at 0 (:26) and only grows (:162-164)
-    ctx->row_first = first; ctx->row_count = count;
+    ctx->row_first = first; ctx->row_count = count; ctx->row_lay_nb = lay_nb > 1 ? lay_nb : 0;
     ctx->have_cooc = true;
     return GE_OK;
 }

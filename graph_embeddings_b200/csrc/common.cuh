@@ -119,7 +119,7 @@ struct ge_ctx {
     int32_t *d_I = nullptr, *d_J = nullptr;
     float* d_X = nullptr;
     int64_t* d_row_off = nullptr;  // row_count+1 offsets when built here (rows contiguous), else null
-    int32_t row_first = 0, row_count = 0;
+    int32_t row_first = 0, row_count = 0, row_lay_nb = 0;  // virtual-id range when row_lay_nb > 1 (ge_vid)
     int64_t bca_overflow_rows = 0;  // rows that needed the global-memory table tier
     int64_t bca_pops = 0, bca_scanned = 0, bca_fetched = 0;
     double bca_seconds = 0;
@@ -136,6 +136,7 @@ struct ge_ctx {
     double* d_cost = nullptr;     // epoch cost accumulator
     bool any_hot = false;         // packed nonzeros carry hub damping exponents
     int32_t keep_count = 0x7fffffff;  // ids occurring at least this often are in the L2-resident set
+    double hub_mass_max = 0;          // largest share of a launch's nonzeros that touch a damped id
     double hub_kmax = 0;              // hottest id: warps of a full wave expected on it at once
     int32_t capped_launches = 0;
     int64_t warp_cap = 0;             // extreme hub present: launches use at most this many warps (ge_warp_cap); 0 = none
@@ -164,12 +165,13 @@ template <typename T>
 int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp_cap);
-int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, bool block_schedule);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
+void ge_advise_result_buffer(void* p, size_t bytes);  // MADV_HUGEPAGE on a large host result buffer
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
   // occurrences from which an id is a hub (damped deltas)
 void ge_keep_counts(ge_ctx* ctx, const int32_t* cnt_i, int64_t ni, double div_i, double share_i, const int32_t* cnt_j, int64_t nj,
                     double div_j, double share_j, int32_t* keep_i, int32_t* keep_j);  // L2-resident set thresholds (raw occurrence counts)
 void ge_store_geometry(ge_ctx* ctx);  // D4, NS, BO, S from cfg
-int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0);
+int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0, int32_t lay_nb = 0, int32_t lay_Bs = 0);
 // sim.cu
 void ge_free_sim(ge_ctx* ctx);
 // api.cu
@@ -179,7 +181,15 @@ int ge_graph_alloc(ge_ctx* ctx, int32_t V, int64_t E_out, int64_t E_in);   // fr
 int ge_graph_validate(ge_ctx* ctx);   // sorted / unique / in-range neighbour lists, monotone offsets (device pass)
 int upload_staged(ge_ctx* ctx, void* dst, const void* src, size_t bytes);   // pageable host -> device through pinned double buffers
 // bca.cu
-int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count);
+// Id layout of the block schedule.  Contiguous (nb <= 1): block b = ids [b*Bs, (b+1)*Bs).  Cyclic: block
+// b = ids {b, b + nb, b + 2nb, ...} — an id-ordered graph (node types in consecutive id ranges, like the
+// DBLP-shaped configs) then puts the same mix of types into every block.  Both are expressed through a
+// "virtual id" under which blocks are contiguous: vid(v) = (v mod nb) * Bs + v div nb, Bs = ceil(V / nb);
+// vids whose inverse is >= V are padding (at most one per block, at its end).
+__host__ __device__ inline int32_t ge_vid(int32_t v, int32_t nb, int32_t Bs) { return nb > 1 ? (v % nb) * Bs + v / nb : v; }
+__host__ __device__ inline int32_t ge_vid_inv(int32_t vid, int32_t nb, int32_t Bs) { return nb > 1 ? vid / Bs + nb * (vid % Bs) : vid; }
+// rows = the `count` virtual ids from `first` on (lay_nb <= 1: plain ids)
+int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb = 0, int32_t lay_Bs = 0);
 void ge_free_cooc(ge_ctx* ctx);
 // dist.cu
 void ge_dist_free(ge_ctx* ctx);

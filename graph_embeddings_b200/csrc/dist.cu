@@ -78,7 +78,9 @@ struct DistState {
     ncclComm_t comm = nullptr;
     int nb = 0, m = 0;            // blocks per side, blocks per rank
     int32_t Bs = 0;               // ids per block
-    int32_t row_base = 0, row_cnt = 0;
+    int32_t row_base = 0, row_cnt = 0;  // first (virtual) id of the rank's rows; REAL rows it owns
+    int32_t layout = 0;               // 0 = contiguous blocks, 1 = cyclic (common.cuh ge_vid)
+    int32_t lay_nb() const { return layout ? nb : 0; }
     int64_t nnz_global = 0;
     std::vector<int64_t> bucket_off;  // m*nb + 1 offsets into d_nzb, bucket = local_rowblock*nb + colblock
     NzEntry* d_nzb = nullptr;         // bucketed nonzeros, block-local indices
@@ -198,6 +200,27 @@ __global__ void bucket_scatter(const int32_t* __restrict__ I, const int32_t* __r
     }
 }
 
+// per bucket: nonzeros that touch an id damped in that bucket's (uncapped) launch, estimated like
+// bucket_scatter does — a row's count spread over nb * P buckets, a column's over the m row blocks.
+// side 0: cnt over the rank's m * Bs rows; side 1: cnt over all nb * Bs columns.
+__global__ void bucket_hot_mass(const int32_t* __restrict__ cnt, int64_t n, int side, int32_t Bs, int32_t nb, int32_t P,
+                                int32_t Hs, int32_t m, const int32_t* __restrict__ hot, unsigned long long* __restrict__ mass) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const int32_t c = cnt[k];
+        if (c == 0) continue;
+        const int blk = (int)(k / Bs);
+        if (side == 0) {
+            const int32_t est = c / (nb * P);
+            for (int q = 0; q < nb * P; q++) { const int b = blk * nb * P + q; if (est >= hot[b]) atomicAdd(mass + b, (unsigned long long)est); }
+        } else {
+            const int32_t est = c / m;
+            const int part = (P > 1 && k - (int64_t)blk * Bs >= Hs) ? 1 : 0;
+            for (int q = 0; q < m; q++) { const int b = (q * nb + blk) * P + part; if (est >= hot[b]) atomicAdd(mass + b, (unsigned long long)est); }
+        }
+    }
+}
+
 // largest occurrence count per row block (P = 1) or per half column block (input of ge_warp_cap)
 __global__ void segment_max(const int32_t* __restrict__ cnt, int64_t n, int32_t Bs, int32_t P, int32_t Hs,
                             int32_t* __restrict__ out) {
@@ -207,6 +230,38 @@ __global__ void segment_max(const int32_t* __restrict__ cnt, int64_t n, int32_t 
         const int blk = (int)(k / Bs);
         const int seg = blk * P + ((P > 1 && k - (int64_t)blk * Bs >= Hs) ? 1 : 0);
         if (c > out[seg]) atomicMax(out + seg, c);   // the plain read only filters
+    }
+}
+
+// COO ids -> virtual ids (in place; the arrays are dropped after bucketing), and the check that every row
+// belongs to this rank: a foreign row would index outside the bucket table
+__global__ void to_virtual_ids(int32_t* __restrict__ I, int32_t* __restrict__ J, int64_t nnz, int32_t lay_nb, int32_t Bs,
+                               int32_t first, int32_t count, int32_t* __restrict__ bad) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const int32_t i = ge_vid(I[k], lay_nb, Bs), j = ge_vid(J[k], lay_nb, Bs);
+        if (i < first || i >= first + count) *bad = 1;
+        I[k] = i; J[k] = j;
+    }
+}
+
+// rows of block b that are real vertices (the rest of its Bs slab rows is padding)
+__host__ __device__ inline int64_t block_rows(int64_t b, int32_t nb, int32_t Bs, int32_t V, int32_t cyclic) {
+    int64_t n = cyclic ? (b < V ? ((int64_t)V - b + nb - 1) / nb : 0) : (int64_t)V - b * Bs;
+    if (n < 0) n = 0;
+    return n > Bs ? Bs : n;
+}
+
+// real ids of the slab rows, block by block (padding skipped): the order ge_dist_extract emits
+__global__ void local_ids(int32_t* __restrict__ out, int32_t m, int32_t rb0, int32_t nb, int32_t Bs, int32_t V, int32_t cyclic) {
+    const int64_t total = (int64_t)m * Bs;
+    for (int64_t l = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; l < total; l += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t k = (int32_t)(l / Bs), t = (int32_t)(l % Bs), rb = rb0 + k;
+        const int64_t id = cyclic ? (int64_t)rb + (int64_t)nb * t : (int64_t)rb * Bs + t;
+        if (id >= V) continue;
+        int64_t before = 0;
+        for (int q = 0; q < k; q++) before += block_rows(rb0 + q, nb, Bs, V, cyclic);
+        out[before + t] = (int32_t)id;
     }
 }
 
@@ -355,8 +410,10 @@ extern "C" int ge_dist_row_range(ge_ctx* ctx, int32_t V, int32_t nblocks, int32_
     if (nblocks < 1 || nblocks > 32 || nblocks % d->world) { ctx->err = "nblocks must be a multiple of the world size (<= 32)"; return GE_ERR_INVALID; }
     const int32_t Bs = (V + nblocks - 1) / nblocks, m = nblocks / d->world;
     int64_t lo = (int64_t)d->rank * m * Bs, hi = lo + (int64_t)m * Bs;
-    if (lo > V) lo = V;
-    if (hi > V) hi = V;
+    if (!d->layout) {   // cyclic: a range of VIRTUAL ids, whole blocks (padding included)
+        if (lo > V) lo = V;
+        if (hi > V) hi = V;
+    }
     if (first) *first = (int32_t)lo;
     if (count) *count = (int32_t)(hi - lo);
     return GE_OK;
@@ -373,7 +430,8 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     int32_t first = 0, count = 0;
     int r = ge_dist_row_range(ctx, ctx->V, nblocks, &first, &count);
     if (r) return r;
-    if (ctx->d_row_off && (ctx->row_first != first || ctx->row_count != count)) {
+    if (ctx->d_row_off && (ctx->row_first != first || ctx->row_count != count || (ctx->row_lay_nb > 1) != (d->layout != 0 && nblocks > 1) ||
+                           (ctx->row_lay_nb > 1 && ctx->row_lay_nb != nblocks))) {
         ctx->err = "co-occurrence rows do not match this rank's block range (use ge_dist_row_range)";
         return GE_ERR_STATE;
     }
@@ -393,6 +451,28 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     d->Hs = d->P > 1 ? (d->Bs + 1) / 2 : d->Bs;
     if (d->m * d->nb * d->P > 1024) { ctx->err = "too many buckets (nblocks^2 / world * 2 must be <= 1024)"; return GE_ERR_INVALID; }
     d->row_base = first; d->row_cnt = count;
+    if (d->layout) {   // real rows among the m * Bs slab rows
+        int64_t n = 0;
+        for (int k = 0; k < d->m; k++) n += block_rows((int64_t)d->rank * d->m + k, nblocks, d->Bs, ctx->V, 1);
+        d->row_cnt = (int32_t)n;
+    }
+    {   // ids -> virtual ids; every row must be one of this rank's
+        int32_t* d_bad = nullptr;
+        GE_CUDA(cudaMalloc(&d_bad, 4));
+        cudaMemsetAsync(d_bad, 0, 4, st);
+        if (ctx->nnz > 0)
+            to_virtual_ids<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->nnz, d->lay_nb(), d->Bs, first, count, d_bad);
+        int32_t bad = 0;
+        cudaError_t e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        cudaFree(d_bad);
+        GE_CUDA(e);
+        if (bad) {
+            ge_free_cooc(ctx);   // the arrays now hold virtual ids: unusable for anything else
+            ctx->err = "a nonzero's row is not one of this rank's rows (ge_dist_row_range / ge_dist_local_ids)";
+            return GE_ERR_INVALID;
+        }
+    }
 
     // global max (f(x) weight uses it, GloveCost.java:19) and global nnz (cost normaliser)
     double* d_tmp = nullptr;
@@ -438,25 +518,38 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         // per bucket: the launch's warp cap (an extreme hub inside it) and, from the warps it then has,
         // the occurrence count from which an id is damped
         d->bucket_cap.assign(nbuckets, 0);
-        ctx->hub_kmax = 0; ctx->capped_launches = 0; ctx->warp_cap = 0;
+        ctx->hub_kmax = 0; ctx->hub_mass_max = 0; ctx->capped_launches = 0; ctx->warp_cap = 0;
         if (!r && flags) {
             int32_t* d_seg = nullptr;
+            int32_t* d_hot0 = nullptr;
+            unsigned long long* d_mass = nullptr;
             const int nseg_i = d->m, nseg_j = d->nb * d->P;
             std::vector<int32_t> seg(nseg_i + nseg_j, 0);
+            std::vector<int32_t> hot0(nbuckets);
+            std::vector<unsigned long long> mass(nbuckets, 0);
+            for (int b = 0; b < nbuckets; b++) hot0[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs, 0);   // uncapped launches
             cudaError_t e = cudaMalloc(&d_seg, seg.size() * 4);
+            if (e == cudaSuccess) e = cudaMalloc(&d_hot0, (size_t)nbuckets * 4);
+            if (e == cudaSuccess) e = cudaMalloc(&d_mass, (size_t)nbuckets * 8);
             if (e == cudaSuccess) e = cudaMemsetAsync(d_seg, 0, seg.size() * 4, st);
+            if (e == cudaSuccess) e = cudaMemsetAsync(d_mass, 0, (size_t)nbuckets * 8, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(d_hot0, hot0.data(), (size_t)nbuckets * 4, cudaMemcpyHostToDevice, st);
             if (e == cudaSuccess) {
                 segment_max<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_i, (int64_t)d->m * d->Bs, d->Bs, 1, 0, d_seg);
                 segment_max<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_j, (int64_t)d->nb * d->Bs, d->Bs, d->P, d->Hs, d_seg + nseg_i);
+                bucket_hot_mass<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_i, (int64_t)d->m * d->Bs, 0, d->Bs, d->nb, d->P, d->Hs, d->m, d_hot0, d_mass);
+                bucket_hot_mass<<<ctx->sm_count * 4, 256, 0, st>>>(cnt_j, (int64_t)d->nb * d->Bs, 1, d->Bs, d->nb, d->P, d->Hs, d->m, d_hot0, d_mass);
                 e = cudaMemcpyAsync(seg.data(), d_seg, seg.size() * 4, cudaMemcpyDeviceToHost, st);
+                if (e == cudaSuccess) e = cudaMemcpyAsync(mass.data(), d_mass, (size_t)nbuckets * 8, cudaMemcpyDeviceToHost, st);
             }
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-            cudaFree(d_seg);
+            cudaFree(d_seg); cudaFree(d_hot0); cudaFree(d_mass);
             if (e != cudaSuccess) { cudaFree(cnt_i); cudaFree(cnt_j); cudaFree(d_cnt); GE_CUDA(e); }
             for (int b = 0; b < nbuckets; b++) {
                 const int lrb = b / (d->nb * d->P), cbp = b % (d->nb * d->P);
                 const int64_t mi = seg[lrb] / (d->nb * d->P), mj = seg[nseg_i + cbp] / d->m;   // bucket_scatter's estimates
-                d->bucket_cap[b] = ge_warp_cap(ctx, (int64_t)hc[b], mi > mj ? mi : mj, true);
+                const double share = hc[b] ? (double)mass[b] / (double)hc[b] : 0.0;
+                d->bucket_cap[b] = ge_warp_cap(ctx, (int64_t)hc[b], mi > mj ? mi : mj, share, true);
                 hot[b] = ge_hot_count(ctx, (int64_t)hc[b], d->Bs, d->bucket_cap[b]);
                 if (d->bucket_cap[b] > 0 && (ctx->warp_cap == 0 || d->bucket_cap[b] < ctx->warp_cap)) ctx->warp_cap = d->bucket_cap[b];  // smallest, for ge_train_hub_info
             }
@@ -505,7 +598,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     d->flags = reinterpret_cast<uint32_t*>(d->d_Cring + (size_t)slots * slab);
     GE_CUDA(cudaMemsetAsync(ctx->d_W, 0, (size_t)d->m * slab * sizeof(float), st));
     GE_CUDA(cudaMemsetAsync(d->d_Cring, 0, (size_t)slots * slab * sizeof(float) + 256, st));
-    r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, count, first);
+    r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, d->layout ? d->m * d->Bs : count, first, d->lay_nb(), d->Bs);
     if (r) return r;
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
     cudaFree(d->d_queue); d->d_queue = nullptr;
@@ -666,15 +759,42 @@ static int dist_extract_impl(ge_ctx* ctx, T* out, int64_t cap) {
     std::vector<const float*> W, C;
     std::vector<int64_t> rows;
     for (int k = 0; k < d->m; k++) {
-        int64_t n = (int64_t)d->row_cnt - (int64_t)k * d->Bs;
-        if (n <= 0) break;
-        if (n > d->Bs) n = d->Bs;
+        const int64_t n = block_rows((int64_t)d->rank * d->m + k, d->nb, d->Bs, ctx->V, d->layout);
+        if (n <= 0) continue;
         W.push_back(ctx->d_W + (size_t)k * slab);
         C.push_back(d->d_Cring + (size_t)((d->head + k) % slots) * slab);
         rows.push_back(n);
     }
+    ge_advise_result_buffer(out, (size_t)d->row_cnt * dim * sizeof(T));
     return ge_extract_blocks<T>(ctx, (int)rows.size(), W.data(), C.data(), rows.data(), out);
 }
+// layout of the block grid: 0 = contiguous id blocks (default), 1 = cyclic (block b = ids b, b + nb, ...);
+// call before ge_dist_row_range / the build / ge_dist_prepare
+extern "C" int ge_dist_set_layout(ge_ctx* ctx, int32_t layout) {
+    if (!ctx || !ctx->dist) { if (ctx) ctx->err = "ge_dist_init first"; return GE_ERR_STATE; }
+    if (layout != 0 && layout != 1) { ctx->err = "layout: 0 contiguous, 1 cyclic"; return GE_ERR_INVALID; }
+    if (ctx->dist->d_nzb && ctx->dist->layout != layout) { ctx->err = "layout is fixed once prepared"; return GE_ERR_STATE; }
+    ctx->dist->layout = layout;
+    return GE_OK;
+}
+
+// real vertex ids of this rank's rows, in the order ge_dist_extract emits them; returns their number
+extern "C" int64_t ge_dist_local_ids(ge_ctx* ctx, int32_t* ids, int64_t cap) {
+    if (!ctx || !ctx->dist || !ctx->dist->d_nzb) { if (ctx) ctx->err = "ge_dist_prepare first"; return GE_ERR_STATE; }
+    DistState* d = ctx->dist;
+    if (!ids || cap < d->row_cnt) { ctx->err = "ge_dist_local_ids: capacity too small"; return GE_ERR_INVALID; }
+    if (d->row_cnt == 0) return 0;
+    cudaSetDevice(ctx->cfg.device);
+    int32_t* dv = nullptr;
+    GE_CUDA(cudaMalloc(&dv, (size_t)d->row_cnt * 4));
+    local_ids<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(dv, d->m, d->rank * d->m, d->nb, d->Bs, ctx->V, d->layout);
+    cudaError_t e = cudaMemcpyAsync(ids, dv, (size_t)d->row_cnt * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dv);
+    GE_CUDA(e);
+    return d->row_cnt;
+}
+
 extern "C" int ge_dist_extract_f32(ge_ctx* ctx, float* out, int64_t cap) { return dist_extract_impl<float>(ctx, out, cap); }
 extern "C" int ge_dist_extract(ge_ctx* ctx, double* out, int64_t cap) { return dist_extract_impl<double>(ctx, out, cap); }
 

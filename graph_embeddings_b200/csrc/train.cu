@@ -13,6 +13,7 @@
 #include <math.h>
 #include <string.h>
 
+#include <sys/mman.h>
 #include <thread>
 
 namespace {
@@ -609,6 +610,15 @@ __global__ void pack_nonzeros(const int32_t* __restrict__ I, const int32_t* __re
     }
 }
 
+// sum of the occurrence counts of the ids at or above `threshold` (nonzeros that touch a damped id)
+__global__ void hot_mass(const int32_t* __restrict__ cnt, int64_t n, int32_t threshold, unsigned long long* __restrict__ out) {
+    unsigned long long m = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) { const int32_t c = cnt[k]; if (c >= threshold) m += (unsigned long long)c; }
+    for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, m);
+}
+
 // largest occurrence count of any id (input of the concurrency cap, ge_warp_cap)
 __global__ void max_count(const int32_t* __restrict__ cnt, int64_t n, int32_t* __restrict__ out) {
     int32_t m = 0;
@@ -631,11 +641,13 @@ __device__ __forceinline__ uint32_t counter24(uint64_t seed, uint64_t idx) {
 
 __global__ void store_init(float* __restrict__ W, float* __restrict__ C, int32_t V, int32_t dim,
                            int32_t D4, int32_t S, int64_t seed, int32_t java, int32_t row0,
-                           int32_t NS, float g0) {
+                           int32_t NS, float g0, int32_t lay_nb, int32_t lay_Bs, int32_t Vglobal) {
     const int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= V) return;
+    const int32_t id = ge_vid_inv(row0 + r, lay_nb, lay_Bs);  // slab row r holds this vertex
+    if (id >= Vglobal) return;                                 // padding row of a cyclic block: stays zero, never addressed
     const uint64_t per_row = 2 + 2 * (uint64_t)dim;
-    const uint64_t first = (uint64_t)(row0 + r) * per_row;  // global draw index of this row
+    const uint64_t first = (uint64_t)id * per_row;  // global draw index of this row
     JavaLcg g = JavaLcg::seeded(seed);
     if (java) g.jump(first);
     uint64_t n = first;
@@ -840,13 +852,13 @@ void ge_store_geometry(ge_ctx* ctx) {
     ctx->S = (ctx->BO + 1 + ctx->NS + 7) & ~7;
 }
 
-// store_init on caller-provided slabs: `rows` rows whose global ids start at row0 (dist.cu)
-int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0) {
+// store_init on caller-provided slabs: `rows` rows whose (virtual, common.cuh ge_vid) ids start at row0 (dist.cu)
+int ge_store_init_rows(ge_ctx* ctx, float* W, float* C, int32_t rows, int32_t row0, int32_t lay_nb, int32_t lay_Bs) {
     const ge_config& c = ctx->cfg;
     if (rows <= 0) return GE_OK;
     store_init<<<(rows + 127) / 128, 128, 0, ctx->stream>>>(W, C, rows, c.dim, ctx->D4, ctx->S, c.seed,
                                                           c.init == GE_INIT_JAVA, row0, ctx->NS,
-                                                          c.opt_method == GE_OPT_ADAGRAD ? 1.0f : 0.0f);
+                                                          c.opt_method == GE_OPT_ADAGRAD ? 1.0f : 0.0f, lay_nb, lay_Bs, ctx->V);
     GE_CUDA(cudaGetLastError());
     return GE_OK;
 }
@@ -969,28 +981,29 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 // nonzeros: on a Zipf(1) matrix (5.5 % on one column, ~260 of the 4 736 resident warps on it) the damped path is
 // 10-30 % off the single-thread loss in the first epoch, and moving such nonzeros into a launch of
 // their own changes the visiting order and with it the online loss (profiles/r02_hubs.md).  The
-// reference never has more writers on a row than threads.  So the launch itself is capped: when the
-// hottest id would have GE_HUB_ONSET (default 64) or more of a full wave's warps on it at once, the
-// launch gets only as many warps as put GE_HUB_SERIAL (default 8) on it; the uniform shuffled order is
-// kept.  Measured vs the single-thread oracle on that matrix, first epoch / later epochs: 16 on the hub
-// 2.0 % / <= 0.6 %, 8 on the hub 0.23 % / <= 0.13 %.  Inside the block schedule's buckets, where the hub
-// is 12-50 % of a launch instead of 5 %, the same count is far less accurate (16: 38 %, 8: 2.0 % /
-// <= 0.4 %), so the buckets use half of it (4: 0.45 % / <= 0.14 % against the oracle walking the block
-// order) and, being 16x more concentrated for any matrix, engage from 4x the onset.  The epoch then runs at the hub's own pace
-// (count x per-nonzero latency / writers), which is what bounded staleness on that row costs.
-// GE_HUB_SERIAL=0 switches the cap off.  Returns 0 = no cap.
-int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, bool block_schedule) {
+// reference never has more writers on a row than threads.  So the launch itself is capped — the uniform
+// shuffled order is kept — to as many warps as put GE_HUB_SERIAL (default 8) on the hottest id.  Measured vs
+// the single-thread oracle on that matrix, first epoch / later epochs: 16 on the hub 2.0 % / <= 0.6 %, 8 on
+// the hub 0.23 % / <= 0.13 %.  Inside the block schedule's buckets, where the hub is 12-50 % of a launch
+// instead of 5 %, the same count is less accurate (16: 38 %, 8: 2.0 % / <= 0.4 %), so the buckets use half
+// of it (4: 0.45 % / <= 0.14 % against the oracle walking the block order).
+// When: the error of damping grows with the share of the launch's nonzeros that touch a damped id, not with
+// the hottest id alone — C4's hottest column has ~85 warps on it inside its buckets but the damped ids hold
+// a few percent of a bucket (damped there, 2.8e-5 from the 1-rank walk); on the Zipf matrix they hold
+// 28 % of the launch and 12-90 % of a bucket.  The cap engages when that share (`hub_mass`, from the id
+// histograms) reaches GE_HUB_MASS (default 0.10).  The epoch then runs at the hub's own pace (count x
+// per-nonzero latency / writers), which is what bounded staleness on that row costs.  GE_HUB_SERIAL=0
+// switches the cap off.  Returns 0 = no cap.
+int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule) {
     double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 8.0;
     if (block_schedule) serial = getenv("GE_HUB_SERIAL_BLOCKS") ? atof(getenv("GE_HUB_SERIAL_BLOCKS")) : 0.5 * serial;
-    // buckets concentrate a column's nonzeros 16x (8 GPUs x 2 halves): C4's hottest column sits at ~85 of a
-    // full wave's warps inside its buckets, damped and checked against the 1-rank walk; Zipf(1) at 2 343
-    double onset = getenv("GE_HUB_ONSET") ? atof(getenv("GE_HUB_ONSET")) : 64.0;
-    if (block_schedule) onset = getenv("GE_HUB_ONSET_BLOCKS") ? atof(getenv("GE_HUB_ONSET_BLOCKS")) : 4.0 * onset;
+    const double theta = getenv("GE_HUB_MASS") ? atof(getenv("GE_HUB_MASS")) : 0.10;
     if (max_count <= 0 || launch_nnz <= 0) return 0;
     const double full = (double)ctx->sm_count * 32.0;
     const double k = full * (double)max_count / (double)launch_nnz;   // warps of a full wave on the hottest id
     if (k > ctx->hub_kmax) ctx->hub_kmax = k;
-    if (serial <= 0 || k < onset || k <= serial) return 0;
+    if (hub_mass > ctx->hub_mass_max) ctx->hub_mass_max = hub_mass;
+    if (serial <= 0 || hub_mass < theta || k <= serial) return 0;
     const double w = serial * (double)launch_nnz / (double)max_count;
     ctx->capped_launches++;
     return w < 1 ? 1 : (int64_t)w;
@@ -998,9 +1011,10 @@ int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, bool blo
 
 // hottest id over all launches shaped since the last prepare: expected concurrent warps on it in an
 // uncapped wave, and how many launches (1 for the single-GPU trainer, buckets for the block schedule) are capped
-extern "C" int ge_train_hub_info(ge_ctx* ctx, double* max_concurrency, int32_t* capped_launches, int64_t* warp_cap) {
+extern "C" int ge_train_hub_info(ge_ctx* ctx, double* max_concurrency, double* damped_share, int32_t* capped_launches, int64_t* warp_cap) {
     if (!ctx) return GE_ERR_INVALID;
     if (max_concurrency) *max_concurrency = ctx->hub_kmax;
+    if (damped_share) *damped_share = ctx->hub_mass_max;
     if (capped_launches) *capped_launches = ctx->capped_launches;
     if (warp_cap) *warp_cap = ctx->warp_cap;
     return GE_OK;
@@ -1022,19 +1036,27 @@ int ge_train_prepare(ge_ctx* ctx) {
         int32_t keep_i, keep_j;
         ge_keep_counts(ctx, cnt_i, ctx->V, 1.0, 1.0, cnt_j, ctx->V, 1.0, 1.0, &keep_i, &keep_j);
         ctx->keep_count = keep_i;
-        int32_t* d_flags = nullptr;   // [0] any damped id, [1] max occurrence count
-        GE_CUDA(cudaMalloc(&d_flags, 8));
-        cudaMemsetAsync(d_flags, 0, 8, ctx->stream);
-        int32_t fl[2] = {0, 0};
+        int32_t* d_flags = nullptr;   // [0] any damped id, [1] max occurrence count, [2..3] u64 damped mass
+        GE_CUDA(cudaMalloc(&d_flags, 16));
+        cudaMemsetAsync(d_flags, 0, 16, ctx->stream);
+        int32_t fl[4] = {0, 0, 0, 0};
         cudaError_t pe = cudaSuccess;
         ctx->warp_cap = 0;
-        ctx->hub_kmax = 0; ctx->capped_launches = 0;
+        ctx->hub_kmax = 0; ctx->hub_mass_max = 0; ctx->capped_launches = 0;
         if (cnt_i) {
+            const int32_t hot0 = ge_hot_count(ctx, ctx->nnz, ctx->V, 0);   // uncapped wave
+            unsigned long long* d_mass = reinterpret_cast<unsigned long long*>(d_flags + 2);
             max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_i, ctx->V, d_flags + 1);
             max_count<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, ctx->V, d_flags + 1);
-            pe = cudaMemcpyAsync(fl, d_flags, 8, cudaMemcpyDeviceToHost, ctx->stream);
+            hot_mass<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_i, ctx->V, hot0, d_mass);
+            hot_mass<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(cnt_j, ctx->V, hot0, d_mass);
+            pe = cudaMemcpyAsync(fl, d_flags, 16, cudaMemcpyDeviceToHost, ctx->stream);
             if (pe == cudaSuccess) pe = cudaStreamSynchronize(ctx->stream);
-            if (pe == cudaSuccess) ctx->warp_cap = ge_warp_cap(ctx, ctx->nnz, fl[1], false);
+            unsigned long long mass = 0;
+            memcpy(&mass, fl + 2, 8);
+            if (pe == cudaSuccess) ctx->warp_cap = ge_warp_cap(ctx, ctx->nnz, fl[1], (double)mass / (double)ctx->nnz, false);
+            fl[0] = 0;
+            if (pe == cudaSuccess) pe = cudaMemsetAsync(d_flags, 0, 4, ctx->stream);
         }
         if (pe == cudaSuccess) {
             pack_nonzeros<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->d_I, ctx->d_J, ctx->d_X, ctx->nnz, c.method,
@@ -1135,6 +1157,15 @@ extern "C" int ge_cost_history(ge_ctx* ctx, double* out, int32_t cap) {
 // first-touch page faults of a freshly allocated destination in parallel).  The device always produces
 // f32 — (float)(f + c) / 2 IS the reference's value (Optimizer.java:130-140) — and the widening to the
 // double[] the seam returns happens in that host pass: half the PCIe bytes, identical bits.
+// The result buffer is fresh anonymous memory of many GB (double[V * dim]): written through 4 KB first-touch
+// faults the host side of the extract ran at ~5 GB/s (2.9 s of a 4.4 s configs[4] job).  Ask for
+// transparent huge pages on the 2 MB-aligned interior; a no-op where THP is off.
+void ge_advise_result_buffer(void* p, size_t bytes) {
+    const uintptr_t huge = (uintptr_t)2 << 20;
+    const uintptr_t a = ((uintptr_t)p + huge - 1) & ~(huge - 1), b = ((uintptr_t)p + bytes) & ~(huge - 1);
+    if (bytes >= ((size_t)64 << 20) && b > a) madvise((void*)a, b - a, MADV_HUGEPAGE);
+}
+
 struct ExtractStage {
     float* d[2] = {nullptr, nullptr};
     float* h[2] = {nullptr, nullptr};
@@ -1209,6 +1240,7 @@ static int extract_impl(ge_ctx* ctx, T* out) {
     if (ctx->dist) { ctx->err = "block-rotation trainer: use ge_dist_extract / ge_dist_extract_f32"; return GE_ERR_STATE; }
     cudaSetDevice(ctx->cfg.device);
     ExtractStage S;
+    ge_advise_result_buffer(out, (size_t)ctx->V * ctx->cfg.dim * sizeof(T));
     cudaError_t e = S.init(ctx->cfg.dim, ctx->V);
     if (e == cudaSuccess) e = extract_rows<T>(ctx, S, ctx->d_W, ctx->d_C, ctx->V, out);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);

@@ -12,11 +12,16 @@ from .api import Configuration, _Native, _ptr
 
 
 class DistTrainer:
-    def __init__(self, config: Configuration, rank: int = 0, world: int = 1, nblocks: int = 8, id_bytes: bytes | None = None):
+    def __init__(self, config: Configuration, rank: int = 0, world: int = 1, nblocks: int = 8, id_bytes: bytes | None = None,
+                 layout: str = "contiguous"):
+        """layout: "contiguous" — block b = ids [b*Bs, (b+1)*Bs); "cyclic" — block b = ids b, b+nblocks, ...
+        (balanced buckets on id-ordered graphs such as the DBLP-shaped configs; profiles/r02_block_balance.md)."""
         self.config, self.rank, self.world, self.nb = config, rank, world, nblocks
         self._n = _Native(config)
         buf = C.create_string_buffer(id_bytes, _lib.NCCL_ID_BYTES) if id_bytes else None
         self._n.ck(self._n.L.ge_dist_init(self._n.h, rank, world, buf))
+        self.layout = {"contiguous": 0, "cyclic": 1}[layout]
+        self._n.ck(self._n.L.ge_dist_set_layout(self._n.h, self.layout))
         self.V = 0
 
     @staticmethod
@@ -28,6 +33,8 @@ class DistTrainer:
         return buf.raw
 
     def row_range(self, V: int):
+        """contiguous layout: this rank's ids [first, first + count).  Cyclic: the same numbers are VIRTUAL ids
+        (whole blocks, padding included) — use owned_ids(V) for the vertices."""
         f, c = C.c_int32(0), C.c_int32(0)
         self._n.ck(self._n.L.ge_dist_row_range(self._n.h, V, self.nb, C.byref(f), C.byref(c)))
         return f.value, c.value
@@ -52,7 +59,10 @@ class DistTrainer:
         self.V = L.ge_vocab_size(n.h)
         first, count = self.row_range(self.V)
         nnz, xmax = C.c_int64(0), C.c_double(0)
-        n.ck(L.ge_cooc_build_rows(n.h, first, count, C.byref(nnz), C.byref(xmax)))
+        if self.layout:
+            n.ck(L.ge_cooc_build_rows_cyclic(n.h, self.nb, first, count, C.byref(nnz), C.byref(xmax)))
+        else:
+            n.ck(L.ge_cooc_build_rows(n.h, first, count, C.byref(nnz), C.byref(xmax)))
         return nnz.value, xmax.value
 
     def import_rows(self, V, I, J, X, xmax=0.0):
@@ -71,20 +81,40 @@ class DistTrainer:
     def prepare(self):
         self._n.ck(self._n.L.ge_dist_prepare(self._n.h, self.nb))
 
+    def owned_ids(self, V: int) -> np.ndarray:
+        """vertex ids whose rows this rank builds / imports / trains, in extraction order (needs no prepare)"""
+        first, count = self.row_range(V)
+        if not self.layout:
+            return np.arange(first, first + count, dtype=np.int32)
+        Bs = (V + self.nb - 1) // self.nb
+        vid = np.arange(first, first + count, dtype=np.int64)
+        ids = vid // Bs + self.nb * (vid % Bs)
+        return ids[ids < V].astype(np.int32)
+
+    def local_ids(self) -> np.ndarray:
+        """the same from the prepared trainer (ge_dist_local_ids)"""
+        out = np.empty(len(self.owned_ids(self.V)), np.int32)
+        n = self._n.L.ge_dist_local_ids(self._n.h, _ptr(out), out.size)
+        if n < 0:
+            self._n.ck(int(n))
+        assert n == out.size
+        return out
+
     def epoch(self) -> float:
         cost = C.c_double(0)
         self._n.ck(self._n.L.ge_dist_train_epoch(self._n.h, C.byref(cost)))
         return cost.value
 
     def extract_local(self) -> np.ndarray:
-        _, count = self.row_range(self.V)
+        """(W + C) / 2 of this rank's rows, f32, row k = vertex owned_ids(V)[k]"""
+        count = len(self.owned_ids(self.V))
         out = np.empty((count, self.config.dim), np.float32)
         self._n.ck(self._n.L.ge_dist_extract_f32(self._n.h, _ptr(out), out.size))
         return out
 
     def extract_local_f64(self) -> np.ndarray:
         """this rank's rows of Optimum.getResult(): double[count * dim] as the seam returns it"""
-        _, count = self.row_range(self.V)
+        count = len(self.owned_ids(self.V))
         out = np.empty((count, self.config.dim), np.float64)
         self._n.ck(self._n.L.ge_dist_extract(self._n.h, _ptr(out), out.size))
         return out
@@ -97,11 +127,11 @@ class DistTrainer:
         self._n.ck(self._n.L.ge_train_stats(self._n.h, C.byref(s), C.byref(l), C.byref(u)))
         rot = {-1: "pointer shift (1 GPU)", 0: "nccl send/recv in-stream", 1: "nccl half blocks, second stream",
                2: "copy engine into the neighbour's IPC-mapped ring"}.get(self._n.L.ge_dist_rotation_mode(self._n.h), "?")
-        k, nc, w = C.c_double(0), C.c_int32(0), C.c_int64(0)
-        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(nc), C.byref(w)))
+        k, sh, nc, w = C.c_double(0), C.c_double(0), C.c_int32(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_train_hub_info(self._n.h, C.byref(k), C.byref(sh), C.byref(nc), C.byref(w)))
         return {"bucket_nnz": b[:n].copy(), "comm_seconds": comm.value, "nnz_global": nnzg.value, "rotation": rot,
                 "update_seconds": s.value, "launches": l.value, "updates": u.value,
-                "hub": {"max_concurrency": k.value, "capped_launches": nc.value, "warp_cap": w.value}}
+                "hub": {"max_concurrency": k.value, "damped_share": sh.value, "capped_launches": nc.value, "warp_cap": w.value}}
 
     def set_stream(self, s):
         self._n.set_stream(s)

@@ -234,13 +234,14 @@ int ge_train_reset(ge_ctx*);
 int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* updates);
 /* Hub report of the prepared trainer (single-GPU or block schedule).  The reference has at most
  * nproc-1 writers on an embedding row (Optimizer.java:84-92); a GPU wave has 4 736 warps.  Ids that
- * would see more than GE_HOT_WRITERS (16) of them get damped deltas; when the hottest id would see
- * GE_HUB_ONSET (64) or more, the launch is capped to the warp count that puts GE_HUB_SERIAL (8; half of
- * it in the buckets of the block schedule) on it.
+ * would see more than GE_HOT_WRITERS (16) of them get damped deltas; when the damped ids hold GE_HUB_MASS
+ * (10 %) or more of a launch's nonzeros, the launch is capped to the warp count that puts GE_HUB_SERIAL
+ * (8; half of it in the buckets of the block schedule) on the hottest id.
  *   max_concurrency : warps of an uncapped wave expected on the hottest id at once
+ *   damped_share    : largest share of a launch's nonzeros that touch a damped id
  *   capped_launches : launches (1, or buckets of the block schedule) that run capped
  *   warp_cap        : the (smallest) cap, 0 = none */
-int ge_train_hub_info(ge_ctx*, double* max_concurrency, int32_t* capped_launches, int64_t* warp_cap);
+int ge_train_hub_info(ge_ctx*, double* max_concurrency, double* damped_share, int32_t* capped_launches, int64_t* warp_cap);
 
 /* SURVEY §8(f) row 2 — EmbeddingTextWriter.write (J/util/write/EmbeddingTextWriter.java:73-149)
  * served from the device store: <vectors_path> gets one line of "%11.6E" values (Java Formatter
@@ -270,6 +271,16 @@ int ge_dist_init(ge_ctx*, int32_t rank, int32_t world, const void* id128);
 /* this rank's id range in an nblocks x nblocks grid over V ids: build exactly these rows
  * (ge_cooc_build_rows) or import nonzeros whose rows lie in it */
 int ge_dist_row_range(ge_ctx*, int32_t V, int32_t nblocks, int32_t* first, int32_t* count);
+/* Id layout of the block grid, to be chosen before ge_dist_row_range / the build / ge_dist_prepare.
+ * 0 = contiguous (block b = ids [b*Bs, (b+1)*Bs), Bs = ceil(V / nblocks)); 1 = cyclic (block b = ids b,
+ * b + nblocks, ...), which balances the buckets of id-ordered graphs (node types in consecutive id ranges, as
+ * Rdf2GrphConverter numbers them in encounter order: J/convert/Rdf2GrphConverter.java).  Cyclic: ge_dist_row_range returns a range of VIRTUAL ids
+ * vid(v) = (v mod nblocks) * Bs + v div nblocks (whole blocks; a vid whose vertex is >= V is padding); build
+ * with ge_cooc_build_rows_cyclic, or import the nonzeros of the rows ge_dist_local_ids lists. */
+int ge_dist_set_layout(ge_ctx*, int32_t layout);
+int ge_cooc_build_rows_cyclic(ge_ctx*, int32_t nblocks, int32_t first_vid, int32_t count, int64_t* nnz, double* xmax);
+/* after ge_dist_prepare: the vertex of every row ge_dist_extract emits, in that order; returns their number */
+int64_t ge_dist_local_ids(ge_ctx*, int32_t* ids, int64_t cap);
 /* all-reduce max()/nnz, bucket the local nonzeros by (row-block, col-block), allocate and
  * initialise this rank's W rows and its ring of C-block slots */
 int ge_dist_prepare(ge_ctx*, int32_t nblocks);

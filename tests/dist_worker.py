@@ -26,28 +26,35 @@ def main():
     cfg = Configuration(method=method, dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=31, device=local)
     idb = [DistTrainer.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(idb, src=0)
-    tr = DistTrainer(cfg, rank, world, 8, idb[0])
+    layout = os.environ.get("GE_TEST_LAYOUT", "contiguous")
+    tr = DistTrainer(cfg, rank, world, 8, idb[0], layout=layout)
     tr.build(g)
     tr.prepare()
     hist = [tr.epoch() for _ in range(epochs)]
     emb = tr.extract_local()
-    first, count = tr.row_range(g.V)
+    ids = tr.local_ids()
+    assert np.array_equal(ids, tr.owned_ids(g.V))
     parts = [None] * world if rank == 0 else None
-    dist.gather_object((first, emb), parts, dst=0)
-    res = {"world": world, "hist": hist, "rotation": tr.stats()["rotation"]}
+    dist.gather_object((ids, emb), parts, dst=0)
+    res = {"world": world, "hist": hist, "rotation": tr.stats()["rotation"], "layout": layout}
     dist.barrier()
     if rank == 0:
         full = np.zeros((g.V, dim), np.float32)
-        for f, e in parts:
-            full[f:f + len(e)] = e
+        seen = np.zeros(g.V, np.int32)
+        for ids_r, e in parts:
+            full[ids_r] = e
+            seen[ids_r] += 1
+        assert (seen == 1).all()                   # the ranks' rows partition the vertices
         single = []
         embs = []
         for rep in range(2):                       # twice: the second run measures Hogwild run-to-run noise
-            t1 = DistTrainer(cfg, 0, 1, 8, None)
+            t1 = DistTrainer(cfg, 0, 1, 8, None, layout=layout)
             t1.build(g)
             t1.prepare()
             single.append([t1.epoch() for _ in range(epochs)])
-            embs.append(t1.extract_local())
+            e1 = np.zeros((g.V, dim), np.float32)
+            e1[t1.local_ids()] = t1.extract_local()
+            embs.append(e1)
             del t1
         a, b = full.astype(np.float64).ravel(), embs[0].astype(np.float64).ravel()
         res.update(single=single[0], single_repeat=single[1],

@@ -56,3 +56,67 @@ def test_block_schedule_loss_matches_reference(method):
     assert emb.shape == (g.V, dim) and np.isfinite(emb).all()
     a, b = emb.astype(np.float64).ravel(), o.extract().ravel()
     assert a @ b / (np.linalg.norm(a) * np.linalg.norm(b)) > 0.9      # same solution up to SGD noise
+
+
+def _schedule_efficiency(B):
+    """upper bound of the schedule's parallel efficiency from the 8x8 bucket sizes: a sub-epoch lasts as
+    long as its fullest bucket (k, (k+s) mod 8)"""
+    nb = B.shape[0]
+    sub = np.array([[B[k, (k + s) % nb] for k in range(nb)] for s in range(nb)])
+    return B.sum() / nb / sub.max(1).sum(), sub.max(1) / sub.mean(1)
+
+
+def test_cyclic_layout_balances_an_id_ordered_graph():
+    """DBLP-shaped graph: vertex ids are ordered by node type (Rdf2GrphConverter numbers nodes in encounter
+    order), so contiguous id blocks give buckets of very different size — a rank with a small bucket idles
+    until the sub-epoch's fullest one is done.  Cyclic blocks (block b = ids b, b+8, ...) hold the same mix
+    of types.  Checked here on one GPU (world = 1 walks the buckets an 8-GPU run walks):
+    the cyclic build yields the oracle's COO bit for bit, the buckets are the ones the layout defines,
+    the loss follows the oracle walking that block order within 1 %, rows come back under their vertex ids."""
+    g = synth.dblp_like(0.1)
+    dim, epochs, nb = 32, 6, 8
+    c = Configuration(method="pglove", dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=31)
+    ref = oracle.cooc_build(g, threads=8)
+    Bs = (g.V + nb - 1) // nb
+    eff = {}
+    for layout in ("contiguous", "cyclic"):
+        t = DistTrainer(c, 0, 1, nb, layout=layout)
+        nnz, xmax = t.build(g)
+        assert nnz == ref.nnz and xmax == ref.max
+        t.prepare()
+        ids = t.local_ids()
+        assert np.array_equal(ids, t.owned_ids(g.V)) and np.array_equal(np.sort(ids), np.arange(g.V))
+        if layout == "cyclic":
+            assert np.array_equal(ids[:4], [0, nb, 2 * nb, 3 * nb])
+            vi, vj = (ref.I % nb) * Bs + ref.I // nb, (ref.J % nb) * Bs + ref.J // nb
+        else:
+            vi, vj = ref.I, ref.J
+        B = np.bincount((vi // Bs) * nb + vj // Bs, minlength=nb * nb)
+        assert np.array_equal(t.stats()["bucket_nnz"], B)
+        eff[layout], ratio = _schedule_efficiency(B.reshape(nb, nb))
+        print(f"{layout}: per-sub-epoch fullest/mean bucket {np.round(ratio, 2)}, schedule efficiency bound {eff[layout]:.3f}")
+        if layout == "contiguous":
+            continue
+        got = np.array([t.epoch() for _ in range(epochs)])
+        Hs = (Bs + 1) // 2
+        bucket = ((vi // Bs) * nb + vj // Bs) * 2 + (vj % Bs >= Hs)
+        srt = np.argsort(bucket, kind="stable")
+        start = np.searchsorted(bucket[srt], np.arange(2 * nb * nb + 1))
+        o = oracle.Trainer(g.V, ref.I, ref.J, ref.X, ref.max, dim, "pglove", 31)
+        rng = np.random.default_rng(1)
+        for _ in range(epochs):
+            order = [rng.permutation(srt[start[b]:start[b + 1]])
+                     for b in ((k * nb + (k + s) % nb) * 2 + p for s in range(nb) for k in range(nb) for p in range(2))]
+            o.set_perm(np.concatenate(order).astype(np.int32))
+            o.epoch(False)
+        hb = o.history_exact()
+        rel = np.abs(got - hb) / hb
+        print("cyclic: rel vs oracle walking the block order", np.round(rel, 5))
+        assert rel.max() < 0.01, rel
+        emb = np.zeros((g.V, dim), np.float32)
+        emb[ids] = t.extract_local()
+        a, b = emb.astype(np.float64).ravel(), o.extract().ravel()
+        assert np.isfinite(emb).all() and a @ b / (np.linalg.norm(a) * np.linalg.norm(b)) > 0.9
+        o.close()
+    assert eff["cyclic"] > 0.85 and eff["cyclic"] > 2 * eff["contiguous"], eff
+

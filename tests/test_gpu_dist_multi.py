@@ -23,9 +23,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run(world, tmp_path, rot=None, V=20000, E=160000, dim=32, epochs=6):
-    out = tmp_path / f"dist_{world}_{rot}.json"
+def _run(world, tmp_path, rot=None, V=20000, E=160000, dim=32, epochs=6, layout="contiguous"):
+    out = tmp_path / f"dist_{world}_{rot}_{layout}.json"
     env = dict(os.environ)
+    env["GE_TEST_LAYOUT"] = layout
     if rot:
         env["GE_DIST_ROT"] = rot
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
@@ -42,13 +43,14 @@ def _worlds():
     return [w for w in (2, 4, 8) if w <= n]
 
 
-@pytest.mark.parametrize("rot", ["ce", "nccl"])
-def test_n_rank_run_matches_one_rank_schedule(tmp_path, rot):
+@pytest.mark.parametrize("rot,layout", [("ce", "contiguous"), ("nccl", "contiguous"), ("ce", "cyclic")])
+def test_n_rank_run_matches_one_rank_schedule(tmp_path, rot, layout):
     worlds = _worlds()
     if not worlds:
         pytest.skip("needs at least 2 GPUs")
     for world in worlds:
-        r = _run(world, tmp_path, rot)
+        r = _run(world, tmp_path, rot, layout=layout)
+        assert r["layout"] == layout
         multi, single, rep = np.array(r["hist"]), np.array(r["single"]), np.array(r["single_repeat"])
         noise = np.abs(rep - single) / single
         rel = np.abs(multi - single) / single

@@ -165,7 +165,7 @@ def test_hub_columns_match_the_oracle():
         if upd == "atomic":
             hub = opt.stats()["hub"]
             print("hub report", hub)
-            assert hub["max_concurrency"] > 200 and hub["capped_launches"] == 1 and 0 < hub["warp_cap"] < 1000
+            assert hub["max_concurrency"] > 200 and hub["damped_share"] > 0.2 and hub["capped_launches"] == 1 and 0 < hub["warp_cap"] < 1000
     c = cfg(dim=dim, seed=31)
     tr = DistTrainer(c, 0, 1, 8, None)
     tr.import_rows(V, I, J, X, xmax=0.2)
