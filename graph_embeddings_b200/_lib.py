@@ -72,7 +72,7 @@ SIGNATURES = {
     "ge_dist_local_ids": (_I64, [_P, _P, _I64]),
     "ge_cooc_stats": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64), C.POINTER(_F64)]),
     "ge_train_hub_info": (C.c_int, [_P, C.POINTER(_F64), C.POINTER(_F64), C.POINTER(_I32), C.POINTER(_I64)]),
-    "ge_cooc_fetched": (C.c_int, [_P, C.POINTER(_I64)]),
+    "ge_cooc_fetched": (C.c_int, [_P, C.POINTER(_I64), C.POINTER(_I64)]),
     "ge_cooc_export": (C.c_int, [_P, _P, _P, _P, _I64]),
     "ge_cooc_import": (C.c_int, [_P, _I32, _I64, _P, _P, _P, _F64]),
     "ge_cooc_count": (_I64, [_P]),

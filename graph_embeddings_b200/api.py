@@ -221,9 +221,9 @@ class BookmarkColoring(CoOccurrenceMatrix):
     def stats(self):
         pops, scanned, sec = C.c_int64(0), C.c_int64(0), C.c_double(0)
         self._n.ck(self._n.L.ge_cooc_stats(self._n.h, C.byref(pops), C.byref(scanned), C.byref(sec)))
-        fetched = C.c_int64(0)
-        self._n.ck(self._n.L.ge_cooc_fetched(self._n.h, C.byref(fetched)))
-        return {"pops": pops.value, "scanned": scanned.value, "fetched": fetched.value, "seconds": sec.value, "nnz": self._nnz}
+        fetched, tier2 = C.c_int64(0), C.c_int64(0)
+        self._n.ck(self._n.L.ge_cooc_fetched(self._n.h, C.byref(fetched), C.byref(tier2)))
+        return {"pops": pops.value, "scanned": scanned.value, "fetched": fetched.value, "tier2_rows": tier2.value, "seconds": sec.value, "nnz": self._nnz}
 
     def graph_csr(self):
         """The hand-off CSR as it sits on the device (validation of ge_set_graph_edges):

@@ -353,9 +353,10 @@ extern "C" int ge_cooc_stats(ge_ctx* ctx, int64_t* pops, int64_t* scanned, doubl
     return GE_OK;
 }
 
-extern "C" int ge_cooc_fetched(ge_ctx* ctx, int64_t* fetched) {
-    if (!ctx || !fetched) return GE_ERR_INVALID;
-    *fetched = ctx->bca_fetched;
+extern "C" int ge_cooc_fetched(ge_ctx* ctx, int64_t* fetched, int64_t* tier2_rows) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (fetched) *fetched = ctx->bca_fetched;
+    if (tier2_rows) *tier2_rows = ctx->bca_overflow_rows;
     return GE_OK;
 }
 

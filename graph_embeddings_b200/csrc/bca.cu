@@ -465,8 +465,14 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
     if (arena_cap < 1024) arena_cap = 1024;
 
     // tier-1 launch geometry
-    const int hcap1_log2 = 10;  // 1024 slots for 512 records
-    const size_t per1 = (((size_t)T1_CAP * 25 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
+    // records per warp in tier 1: fewer records = more resident warps for this latency-bound kernel, but more
+    // rows that overflow into tier 2 and run twice (GE_BCA_T1_CAP, sweep in profiles/r02_bca_t1cap.md)
+    int t1_cap = getenv("GE_BCA_T1_CAP") ? atoi(getenv("GE_BCA_T1_CAP")) : T1_CAP;
+    t1_cap = t1_cap < 32 ? 32 : (t1_cap > 2040 ? 2040 : t1_cap);
+    t1_cap &= ~7;   // keeps every array of the table 8-byte aligned
+    int hcap1_log2 = 6;
+    while ((1 << hcap1_log2) < 2 * t1_cap) hcap1_log2++;   // index at most half full
+    const size_t per1 = (((size_t)t1_cap * 25 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
     const size_t smem1 = per1 * T1_WARPS;
     GE_CUDA(cudaFuncSetAttribute(bca_push<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     int bps1 = 1;
@@ -503,7 +509,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
         P.work = round == 0 ? nullptr : work.as<int32_t>();
         P.nwork = nwork;
         // ---- tier 1: shared-memory tables
-        P.cap = T1_CAP; P.hcap_log2 = hcap1_log2; P.scratch = nullptr; P.scratch_per_warp = 0;
+        P.cap = t1_cap; P.hcap_log2 = hcap1_log2; P.scratch = nullptr; P.scratch_per_warp = 0;
         {
             int64_t blocks = ((int64_t)nwork + T1_WARPS - 1) / T1_WARPS;
             const int64_t full = (int64_t)ctx->sm_count * bps1;

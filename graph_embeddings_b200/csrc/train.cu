@@ -989,15 +989,15 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 // of it (4: 0.45 % / <= 0.14 % against the oracle walking the block order).
 // When: the error of damping grows with the share of the launch's nonzeros that touch a damped id, not with
 // the hottest id alone — C4's hottest column has ~85 warps on it inside its buckets but the damped ids hold
-// a few percent of a bucket (damped there, 2.8e-5 from the 1-rank walk); on the Zipf matrix they hold
-// 28 % of the launch and 12-90 % of a bucket.  The cap engages when that share (`hub_mass`, from the id
-// histograms) reaches GE_HUB_MASS (default 0.10).  The epoch then runs at the hub's own pace (count x
+// at most 3.2 % of a bucket (damped there, 2.8e-5 from the 1-rank walk); on the Zipf matrix they hold
+// 25 % of the launch and up to 66 % of a bucket.  The cap engages when that share (`hub_mass`, from the id
+// histograms) reaches GE_HUB_MASS (default 0.05).  The epoch then runs at the hub's own pace (count x
 // per-nonzero latency / writers), which is what bounded staleness on that row costs.  GE_HUB_SERIAL=0
 // switches the cap off.  Returns 0 = no cap.
 int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule) {
     double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 8.0;
     if (block_schedule) serial = getenv("GE_HUB_SERIAL_BLOCKS") ? atof(getenv("GE_HUB_SERIAL_BLOCKS")) : 0.5 * serial;
-    const double theta = getenv("GE_HUB_MASS") ? atof(getenv("GE_HUB_MASS")) : 0.10;
+    const double theta = getenv("GE_HUB_MASS") ? atof(getenv("GE_HUB_MASS")) : 0.05;
     if (max_count <= 0 || launch_nnz <= 0) return 0;
     const double full = (double)ctx->sm_count * 32.0;
     const double k = full * (double)max_count / (double)launch_nnz;   // warps of a full wave on the hottest id

@@ -198,8 +198,9 @@ int ge_cooc_build_rows(ge_ctx*, int32_t first, int32_t count, int64_t* nnz, doub
 /* counters of the last build: pops (pair events), scanned adjacency entries, seconds on device */
 int ge_cooc_stats(ge_ctx*, int64_t* pops, int64_t* scanned, double* seconds);
 /* adjacency entries the last build really read: `scanned` counts every entry the reference's loop visits
- * (DirectedWeighted.java:79-98); lists whose heaviest edge cannot reach epsilon are skipped unread here */
-int ge_cooc_fetched(ge_ctx*, int64_t* fetched);
+ * (DirectedWeighted.java:79-98); lists whose heaviest edge cannot reach epsilon are skipped unread here.
+ * tier2_rows: bookmarks whose record table outgrew shared memory and were re-run on a global-memory table */
+int ge_cooc_fetched(ge_ctx*, int64_t* fetched, int64_t* tier2_rows);
 
 /* A6 — cIdx_I/J/C for all k (unpermuted); cap = capacity of the three arrays. */
 int ge_cooc_export(ge_ctx*, int32_t* I, int32_t* J, float* X, int64_t cap);
@@ -235,7 +236,7 @@ int ge_train_stats(ge_ctx*, double* update_seconds, int64_t* launches, int64_t* 
 /* Hub report of the prepared trainer (single-GPU or block schedule).  The reference has at most
  * nproc-1 writers on an embedding row (Optimizer.java:84-92); a GPU wave has 4 736 warps.  Ids that
  * would see more than GE_HOT_WRITERS (16) of them get damped deltas; when the damped ids hold GE_HUB_MASS
- * (10 %) or more of a launch's nonzeros, the launch is capped to the warp count that puts GE_HUB_SERIAL
+ * (5 %) or more of a launch's nonzeros, the launch is capped to the warp count that puts GE_HUB_SERIAL
  * (8; half of it in the buckets of the block schedule) on the hottest id.
  *   max_concurrency : warps of an uncapped wave expected on the hottest id at once
  *   damped_share    : largest share of a launch's nonzeros that touch a damped id

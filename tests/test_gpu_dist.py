@@ -21,6 +21,7 @@ def test_block_schedule_loss_matches_reference(method):
     assert nnz == ref.nnz and xmax == ref.max
     t.prepare()
     st = t.stats()
+    print("hub report", st["hub"])
     assert st["nnz_global"] == nnz and st["bucket_nnz"].sum() == nnz and len(st["bucket_nnz"]) == 64
     # bucket (rb, cb) holds exactly the nonzeros with i in row-block rb and j in col-block cb
     Bs = (g.V + 7) // 8
