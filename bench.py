@@ -128,7 +128,12 @@ def cpu_baseline(g, dim, steps, warmup, threads, target_nnz=12_000_000):
     if psutil.virtual_memory().available < need:     # shrink the store, fold columns into it
         V = int(psutil.virtual_memory().available / ((8 * dim + 8) * 4 * 1.5))
     J = c.J if V == g.V else (c.J % V).astype(np.int32)
-    I = c.I if V == g.V else (c.I % V).astype(np.int32)
+    # the sample's bookmarks are ids 0..rows: spread them over the whole store (a bijection of the ids), so
+    # that the W side misses the caches like the full workload's does instead of staying in ~100 k hot rows
+    mult = 2654435761
+    while np.gcd(mult, V) != 1:
+        mult += 2
+    I = ((c.I.astype(np.int64) % V) * mult % V).astype(np.int32)
     tr = oracle.Trainer(V, I, J, c.X, c.max, dim, "glove", 12345, threads=threads)
     for _ in range(warmup):
         tr.epoch()
@@ -140,8 +145,9 @@ def cpu_baseline(g, dim, steps, warmup, threads, target_nnz=12_000_000):
     log(f"[bench] cpu baseline: sample rows={rows} nnz={c.nnz} build {build_s:.2f}s ({c.pops / build_s / 1e6:.2f} Mpops/s) "
         f"train {steps} epochs {dt:.2f}s total {time.time() - t0:.1f}s")
     return {"value": c.nnz * steps / dt, "unit": "nnz_updates/s", "cores": threads, "kind": "port",
-            "sample": f"co-occurrence rows of the first {rows} bookmarks ({c.nnz} nonzeros) x {steps} epochs, "
-                      f"store V={V} d={dim}; C++ restatement of the Java path, Hogwild threads={threads}",
+            "sample": f"co-occurrence rows of the first {rows} bookmarks ({c.nnz} nonzeros; row ids spread over the "
+                      f"whole store by an id bijection) x {steps} epochs, store V={V} d={dim}; C++ restatement of the "
+                      f"Java path, Hogwild threads={threads}",
             "cooc_pairs_per_s": c.pops / build_s, "ms_per_step": dt / steps * 1e3, "sample_nnz": int(c.nnz)}
 
 
@@ -163,8 +169,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": "glove_nnz_updates_per_sec", "value": cb["value"], "unit": "nnz_updates/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "alpha": ALPHA, "epsilon": EPS, "dim": dim, "method": "glove",
-                       "optimizer": "adagrad"},
+            "config": {"workload": desc, "V": g.V, "E": g.E, "dim": dim, "alpha": ALPHA, "epsilon": EPS, "method": "glove",
+                       "optimizer": "adagrad", "math": "the reference's arithmetic (fp64 islands), Hogwild plain stores",
+                       "sample_nnz": cb["sample_nnz"]},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "cooc_pairs_per_s": cb["cooc_pairs_per_s"],
             "e2e": {"value": cb["value"], "unit": "nnz_updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
