@@ -18,6 +18,8 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstring>
 
 namespace {
@@ -510,6 +512,7 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
         P.nwork = nwork;
         // ---- tier 1: shared-memory tables
         P.cap = t1_cap; P.hcap_log2 = hcap1_log2; P.scratch = nullptr; P.scratch_per_warp = 0;
+        const auto tick0 = std::chrono::steady_clock::now();
         {
             int64_t blocks = ((int64_t)nwork + T1_WARPS - 1) / T1_WARPS;
             const int64_t full = (int64_t)ctx->sm_count * bps1;
@@ -521,13 +524,17 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
             ctx->err = std::string("bca_push tier 1: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
         }
         const int32_t n_over = h[1];
+        const auto tick1 = std::chrono::steady_clock::now();
         if (n_over > 0) {
             // ---- tier 2: global-memory tables sized by the bound, for the rows that overflowed
             overflow_rows += n_over;
             int hl = 1;
             while (((int64_t)1 << hl) < 2 * cap2) hl++;
             const size_t per2 = (((size_t)cap2 * 29 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
-            int64_t warps = (int64_t)ctx->sm_count * 16;
+            // resident warps: 72 registers allow 28 per SM (GE_BCA_T2_WARPS per SM; sweep in profiles/r02_bca_t1cap.md)
+            int t2_per_sm = getenv("GE_BCA_T2_WARPS") ? atoi(getenv("GE_BCA_T2_WARPS")) : 16;
+            t2_per_sm = t2_per_sm < 2 ? 2 : (t2_per_sm > 64 ? 64 : t2_per_sm);
+            int64_t warps = (int64_t)ctx->sm_count * t2_per_sm;
             if (warps > n_over) warps = n_over;
             size_t fb = 0, tb = 0;
             cudaMemGetInfo(&fb, &tb);
@@ -552,6 +559,10 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
             if (h[1] != 0) { ctx->err = "internal: BCA record bound exceeded"; rc = GE_ERR_CUDA; break; }
         }
         const int32_t n_def = h[2];
+        if (getenv("GE_DEBUG"))
+            fprintf(stderr, "[bca] round %d: %d rows, tier 1 (%d records/warp, %d blocks/SM) %.1f ms, tier 2 %d rows %.1f ms, deferred %d\n",
+                    round, nwork, t1_cap, bps1, std::chrono::duration<double, std::milli>(tick1 - tick0).count(), n_over,
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tick1).count(), n_def);
         if (n_def > 0) {
             if (!work.p && cudaMalloc(&work.p, (size_t)count * 4) != cudaSuccess) { cudaGetLastError(); rc = GE_ERR_NOMEM; ctx->err = "out of device memory"; break; }
             if (cudaMemcpyAsync(work.p, P.deferred, (size_t)n_def * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {

@@ -12,7 +12,9 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("method", ["glove", "pglove"])
 def test_block_schedule_loss_matches_reference(method):
-    g = synth.rmat(8000, 64000, 4)
+    # 20 000 nodes: on 8 000 (1 000-row blocks, 62 warps per launch) two GPU runs of epoch 2 differ from one another
+    # by up to 1 % (Hogwild collisions on a tiny block), which is the bar
+    g = synth.rmat(20000, 160000, 4)
     dim, epochs = 32, 8
     c = Configuration(method=method, dim=dim, bca=BCA(0.1, 1e-3, True), opt=Opt("adagrad", 0.0, epochs), seed=31)
     t = DistTrainer(c, 0, 1, 8)
