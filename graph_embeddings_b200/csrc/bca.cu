@@ -25,7 +25,7 @@
 namespace {
 
 constexpr uint32_t INACTIVE = 0x80000000u;
-constexpr int T1_CAP = 472;          // tier-1 records per warp (shared memory): 25 B each + 2 KB index -> 8 blocks of 2 warps per SM
+constexpr int T1_CAP = 104;          // tier-1 records per warp (shared memory): 25 B each + 512 B index -> 16 blocks of 2 warps per SM (register-bound)
 constexpr int T1_WARPS = 2;          // warps per block in tier 1
 constexpr int MAX_ARENAS = 8;
 
@@ -94,6 +94,12 @@ struct Table {
             if ((key[h - 1] & ~INACTIVE) == id) return (int)h - 1;
             s = (s + 1) & hmask;
         }
+    }
+    // slot that holds record `rec` (it is in the index)
+    __device__ __forceinline__ uint32_t slot_of(int rec) const {
+        uint32_t s = slot0(key[rec] & ~INACTIVE);
+        while (hash[s] != (HT)(rec + 1)) s = (s + 1) & hmask;
+        return s;
     }
     __device__ __forceinline__ void insert(uint32_t id, int rec) {
         uint32_t s = slot0(id);
@@ -214,8 +220,10 @@ __device__ int bca_pass(const BcaParams& P, Table<HT>& T, int n, int pass, int l
     return n;
 }
 
-template <typename HT, bool SMEM>
-__global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
+// MINB = resident blocks per SM the register allocation must allow (tier 2 trades a few spilled
+// registers for more warps in flight: 16 -> 64 registers, 24 -> 40, 32 -> 32)
+template <typename HT, bool SMEM, int MINB = 1>
+__global__ void __launch_bounds__(T1_WARPS * 32, MINB) bca_push(BcaParams P) {
     extern __shared__ __align__(16) uint8_t smem[];
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -338,7 +346,16 @@ __global__ void __launch_bounds__(T1_WARPS * 32) bca_push(BcaParams P) {
         } else {
             pops -= bp; scanned -= bs; fetched -= bf;  // will be recounted when the row is re-run
         }
-        for (int s = lane; s < hwords; s += 32) hwipe[s] = 0;  // wipe the index
+        // wipe the index.  Tier 2's index is 256 KB per warp (65 536 slots for the 20 002-record bound): zeroing
+        // all of it after every row wrote 0.5 TB at C4 — clear the n used slots instead (found read-only first,
+        // because clearing while other lanes still probe would cut their chains; `act` is free by now)
+        if (SMEM) {
+            for (int s = lane; s < hwords; s += 32) hwipe[s] = 0;
+        } else {
+            for (int r = lane; r < n; r += 32) T.act[r] = (HT)T.slot_of(r);
+            __syncwarp();
+            for (int r = lane; r < n; r += 32) T.hash[T.act[r]] = 0;
+        }
         __syncwarp();
     }
     if (lane == 0) {
@@ -476,9 +493,9 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
     while ((1 << hcap1_log2) < 2 * t1_cap) hcap1_log2++;   // index at most half full
     const size_t per1 = (((size_t)t1_cap * 25 + ((size_t)1 << hcap1_log2) * 2) + 15) & ~(size_t)15;
     const size_t smem1 = per1 * T1_WARPS;
-    GE_CUDA(cudaFuncSetAttribute(bca_push<uint16_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    GE_CUDA(cudaFuncSetAttribute(bca_push<uint16_t, true, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     int bps1 = 1;
-    GE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps1, bca_push<uint16_t, true>, T1_WARPS * 32, smem1));
+    GE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps1, bca_push<uint16_t, true, 16>, T1_WARPS * 32, smem1));
     if (bps1 < 1) bps1 = 1;
 
     ArenaSet AS{};
@@ -517,22 +534,31 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
             int64_t blocks = ((int64_t)nwork + T1_WARPS - 1) / T1_WARPS;
             const int64_t full = (int64_t)ctx->sm_count * bps1;
             if (blocks > full) blocks = full;
-            bca_push<uint16_t, true><<<(unsigned)blocks, T1_WARPS * 32, smem1, st>>>(P);
+            bca_push<uint16_t, true, 16><<<(unsigned)blocks, T1_WARPS * 32, smem1, st>>>(P);
         }
         int32_t h[3];
         if (cudaMemcpyAsync(h, d32, 12, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
             ctx->err = std::string("bca_push tier 1: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
         }
-        const int32_t n_over = h[1];
+        int32_t n_over = h[1];
         const auto tick1 = std::chrono::steady_clock::now();
-        if (n_over > 0) {
-            // ---- tier 2: global-memory tables sized by the bound, for the rows that overflowed
-            overflow_rows += n_over;
+        int32_t tier_rows[2] = {0, 0};
+        double tier_ms[2] = {0, 0};
+        // ---- global-memory tiers for the rows that overflowed: a mid tier with small tables (they stay
+        // L2-resident: 64 warps/SM x 36 KB), then tables sized by the bound 2/(alpha*eps) for the few that remain
+        int64_t mid_cap = getenv("GE_BCA_MID_CAP") ? atoll(getenv("GE_BCA_MID_CAP")) : 0;
+        if (mid_cap >= cap2 || mid_cap <= t1_cap) mid_cap = 0;   // 0 = no mid tier
+        overflow_rows += n_over;
+        for (int tier = mid_cap ? 0 : 1; tier < 2 && n_over > 0 && rc == GE_OK; tier++) {
+            const auto tk = std::chrono::steady_clock::now();
+            const int64_t capt = tier == 0 ? mid_cap : cap2;
             int hl = 1;
-            while (((int64_t)1 << hl) < 2 * cap2) hl++;
-            const size_t per2 = (((size_t)cap2 * 29 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
-            // resident warps: 72 registers allow 28 per SM (GE_BCA_T2_WARPS per SM; sweep in profiles/r02_bca_t1cap.md)
-            int t2_per_sm = getenv("GE_BCA_T2_WARPS") ? atoi(getenv("GE_BCA_T2_WARPS")) : 16;
+            while (((int64_t)1 << hl) < 2 * capt) hl++;
+            const size_t per2 = (((size_t)capt * 29 + ((size_t)1 << hl) * 4) + 15) & ~(size_t)15;
+            // resident warps per SM (GE_BCA_T2_WARPS): 64 registers allow 32, 40 allow 48, 32 allow 64 — the kernel
+            // is bound by the latency of its dependent loads, and a few spilled registers cost less than idle
+            // issue slots (sweep in profiles/r02_bca_tiers.md)
+            int t2_per_sm = getenv("GE_BCA_T2_WARPS") ? atoi(getenv("GE_BCA_T2_WARPS")) : 64;
             t2_per_sm = t2_per_sm < 2 ? 2 : (t2_per_sm > 64 ? 64 : t2_per_sm);
             int64_t warps = (int64_t)ctx->sm_count * t2_per_sm;
             if (warps > n_over) warps = n_over;
@@ -541,28 +567,35 @@ int ge_bca_build(ge_ctx* ctx, int32_t first, int32_t count, int32_t lay_nb, int3
             while (warps > 1 && (double)warps * (double)per2 > (double)fb * 0.5) warps /= 2;
             DevBuf scratch, list;
             if (cudaMalloc(&scratch.p, (size_t)warps * per2) != cudaSuccess || cudaMalloc(&list.p, (size_t)n_over * 4) != cudaSuccess) {
-                cudaGetLastError(); ctx->err = "out of device memory for tier-2 BCA tables"; rc = GE_ERR_NOMEM; break;
+                cudaGetLastError(); ctx->err = "out of device memory for global-memory BCA tables"; rc = GE_ERR_NOMEM; break;
             }
             if (cudaMemcpyAsync(list.p, P.overflow, (size_t)n_over * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess ||
                 cudaMemsetAsync(d32, 0, 8, st) != cudaSuccess) {  // next, n_overflow (n_deferred keeps counting)
-                ctx->err = std::string("bca tier-2 set-up: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
+                ctx->err = std::string("bca global tier set-up: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
             }
             BcaParams Q = P;
             Q.work = list.as<int32_t>(); Q.nwork = n_over;
-            Q.cap = (int32_t)cap2; Q.hcap_log2 = hl;
+            Q.cap = (int32_t)capt; Q.hcap_log2 = hl;
             Q.scratch = scratch.as<uint8_t>(); Q.scratch_per_warp = per2; Q.ntables = (int32_t)warps;
             const int64_t blocks = (warps + T1_WARPS - 1) / T1_WARPS;
-            bca_push<uint32_t, false><<<(unsigned)blocks, T1_WARPS * 32, 0, st>>>(Q);
+            if (t2_per_sm <= 32) bca_push<uint32_t, false, 16><<<(unsigned)blocks, T1_WARPS * 32, 0, st>>>(Q);
+            else if (t2_per_sm <= 48) bca_push<uint32_t, false, 24><<<(unsigned)blocks, T1_WARPS * 32, 0, st>>>(Q);
+            else bca_push<uint32_t, false, 32><<<(unsigned)blocks, T1_WARPS * 32, 0, st>>>(Q);
             if (cudaMemcpyAsync(h, d32, 12, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
-                ctx->err = std::string("bca_push tier 2: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
+                ctx->err = std::string("bca_push global tier: ") + cudaGetErrorString(cudaGetLastError()); rc = GE_ERR_CUDA; break;
             }
-            if (h[1] != 0) { ctx->err = "internal: BCA record bound exceeded"; rc = GE_ERR_CUDA; break; }
+            tier_rows[tier] = n_over;
+            tier_ms[tier] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tk).count();
+            n_over = h[1];
+            if (tier == 1 && n_over != 0) { ctx->err = "internal: BCA record bound exceeded"; rc = GE_ERR_CUDA; break; }
         }
+        if (rc) break;
         const int32_t n_def = h[2];
         if (getenv("GE_DEBUG"))
-            fprintf(stderr, "[bca] round %d: %d rows, tier 1 (%d records/warp, %d blocks/SM) %.1f ms, tier 2 %d rows %.1f ms, deferred %d\n",
-                    round, nwork, t1_cap, bps1, std::chrono::duration<double, std::milli>(tick1 - tick0).count(), n_over,
-                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tick1).count(), n_def);
+            fprintf(stderr, "[bca] round %d: %d rows, shared tier (%d records/warp, %d blocks/SM) %.1f ms, mid tier (%lld records) %d rows %.1f ms, "
+                            "bound tier %d rows %.1f ms, deferred %d\n",
+                    round, nwork, t1_cap, bps1, std::chrono::duration<double, std::milli>(tick1 - tick0).count(), (long long)mid_cap,
+                    tier_rows[0], tier_ms[0], tier_rows[1], tier_ms[1], n_def);
         if (n_def > 0) {
             if (!work.p && cudaMalloc(&work.p, (size_t)count * 4) != cudaSuccess) { cudaGetLastError(); rc = GE_ERR_NOMEM; ctx->err = "out of device memory"; break; }
             if (cudaMemcpyAsync(work.p, P.deferred, (size_t)n_def * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
