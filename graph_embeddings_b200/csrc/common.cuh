@@ -4,6 +4,9 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -165,6 +168,18 @@ template <typename T>
 int ge_extract_blocks(ge_ctx* ctx, int nblocks, const float* const* W, const float* const* C, const int64_t* rows, T* out);
 int ge_count_ids(ge_ctx* ctx, const int32_t* d_ids, int64_t nnz, int32_t base, int64_t n, int32_t** d_cnt);
 int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp_cap);
+// GE_DEBUG stopwatch: lap("name") synchronises the stream and prints the time since the previous lap
+struct GeLap {
+    cudaStream_t st; const char* what; bool on; std::chrono::steady_clock::time_point t;
+    GeLap(cudaStream_t s, const char* w) : st(s), what(w), on(getenv("GE_DEBUG") != nullptr), t(std::chrono::steady_clock::now()) {}
+    void lap(const char* name) {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        const auto n = std::chrono::steady_clock::now();
+        fprintf(stderr, "[%s] %-28s %8.1f ms\n", what, name, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
 void ge_advise_result_buffer(void* p, size_t bytes);  // MADV_HUGEPAGE on a large host result buffer
 int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule);  // warps a launch may use when one id holds max_count of its nonzeros (0 = no cap)
   // occurrences from which an id is a hub (damped deltas)

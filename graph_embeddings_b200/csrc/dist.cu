@@ -474,6 +474,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         }
     }
 
+    GeLap lap(st, "dist prepare");
     // global max (f(x) weight uses it, GloveCost.java:19) and global nnz (cost normaliser)
     double* d_tmp = nullptr;
     GE_CUDA(cudaMalloc(&d_tmp, 16));
@@ -498,6 +499,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     GE_CUDA(cudaMalloc(&d_cnt, 1024 * 8));
     GE_CUDA(cudaMemsetAsync(d_cnt, 0, 1024 * 8, st));
     if (ctx->nnz > 0)
+        lap.lap("ids + all-reduces");
         bucket_count<<<ctx->sm_count * 4, 256, 0, st>>>(ctx->d_I, ctx->d_J, ctx->nnz, first, d->Bs, d->nb, d->P, d->Hs, d_cnt);
     std::vector<unsigned long long> hc(1024);
     GE_CUDA(cudaMemcpyAsync(hc.data(), d_cnt, 1024 * 8, cudaMemcpyDeviceToHost, st));
@@ -573,6 +575,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
         if (e != cudaSuccess) { cudaFree(d_cnt); GE_CUDA(e); }
     }
     cudaFree(d_cnt);
+    lap.lap("histograms + bucketing");
     // the COO arrays are no longer needed on the device once bucketed
     cudaFree(ctx->d_I); cudaFree(ctx->d_J); cudaFree(ctx->d_X);
     ctx->d_I = ctx->d_J = nullptr; ctx->d_X = nullptr;
@@ -598,7 +601,9 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     d->flags = reinterpret_cast<uint32_t*>(d->d_Cring + (size_t)slots * slab);
     GE_CUDA(cudaMemsetAsync(ctx->d_W, 0, (size_t)d->m * slab * sizeof(float), st));
     GE_CUDA(cudaMemsetAsync(d->d_Cring, 0, (size_t)slots * slab * sizeof(float) + 256, st));
+    lap.lap("frees + store allocation");
     r = ge_store_init_rows(ctx, ctx->d_W, d->d_Cring, d->layout ? d->m * d->Bs : count, first, d->lay_nb(), d->Bs);
+    lap.lap("store init");
     if (r) return r;
     if (!ctx->d_cost) GE_CUDA(cudaMalloc(&ctx->d_cost, sizeof(double)));
     cudaFree(d->d_queue); d->d_queue = nullptr;
@@ -606,6 +611,7 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     if (d->world > 1 && d->rot == ROT_CE) {
         r = dist_map_peers(ctx);
         if (r) return r;
+        lap.lap("IPC mapping of the rings");
     }
     d->head = 0; d->sub = 0;
     ctx->epoch = 0;
@@ -809,6 +815,7 @@ extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const
     const bool me = d->rank == root;
     cudaSetDevice(ctx->cfg.device);
     cudaStream_t st = ctx->stream;
+    GeLap lap(st, "dist hand-off");
     long long hdr[4] = {0, 0, 0, 0};  // V, E_out, E_in, ok
     if (me) {
         const bool ok = V > 0 && out_off && in_off && out_off[V] >= 0 && in_off[V] >= 0 &&
@@ -825,8 +832,10 @@ extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const
     GE_CUDA(e);
     GE_NCCL(nr);
     if (!hdr[3]) { ctx->err = "bad graph arguments on the root rank"; return GE_ERR_INVALID; }
+    lap.lap("header broadcast");
     int r = ge_graph_alloc(ctx, (int32_t)hdr[0], hdr[1], hdr[2]);
     if (r) { ge_free_graph(ctx); return r; }
+    lap.lap("device allocation");
     const size_t ob = (size_t)(ctx->V + 1) * sizeof(int64_t);
     const struct { void* dv; const void* h; size_t n; } parts[] = {
         {ctx->d_out_off, out_off, ob}, {ctx->d_in_off, in_off, ob},
@@ -837,10 +846,14 @@ extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const
         if (me) { r = upload_staged(ctx, q.dv, q.h, q.n); if (r) { ge_free_graph(ctx); return r; } }
         GE_NCCL(g_nccl.Broadcast(q.dv, q.dv, q.n, NCCL_UINT8, root, d->comm, st));
     }
+    lap.lap("H2D on root + broadcasts");
     ctx->graph_seconds = 0;
     r = ge_graph_validate(ctx);
     if (r) return r;
-    return ge_graph_finish(ctx);
+    lap.lap("CSR validation");
+    r = ge_graph_finish(ctx);
+    lap.lap("node totals / wmax");
+    return r;
 }
 
 // data plane of the rotation actually in use: 0 = NCCL send/recv in the compute stream, 1 = half-block
