@@ -79,14 +79,16 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
     extract_ok = psutil.virtual_memory().available > 2.5 * need * world
     if extract_ok:
         emb = tr.extract_local_f64()               # what the seam returns: this rank's rows of double[V * dim]
-        assert np.isfinite(emb).all()
         d2h = emb.size * 4 + 8 * K                 # f32 crosses PCIe; widened on the host
-        del emb
     else:
+        emb = None
         d2h = 8 * K
     tp = mark("extract", tp)
     barrier()
     t_e2e = time.time() - t0
+    if emb is not None:                            # checked outside the timed region (a 5 GB scan on one host thread)
+        assert np.isfinite(emb).all()
+        del emb
     cst = tr.cooc_stats()
     st0 = tr.stats()
     nnz = st0["nnz_global"]

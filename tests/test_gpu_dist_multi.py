@@ -40,7 +40,8 @@ def _run(world, tmp_path, rot=None, V=20000, E=160000, dim=32, epochs=6, layout=
 def _worlds():
     import torch
     n = torch.cuda.device_count()
-    return [w for w in (2, 4, 8) if w <= n]
+    only = os.environ.get("GE_TEST_WORLDS")        # e.g. "8": one world size per (expensive) 8-GPU call
+    return [w for w in (2, 4, 8) if w <= n and (not only or str(w) in only.split(","))]
 
 
 @pytest.mark.parametrize("rot,layout", [("ce", "contiguous"), ("nccl", "contiguous"), ("ce", "cyclic")])
