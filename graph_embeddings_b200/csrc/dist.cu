@@ -378,7 +378,14 @@ extern "C" int ge_dist_init(ge_ctx* ctx, int32_t rank, int32_t world, const void
         if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
         NcclId id;
         memcpy(&id, id128, GE_NCCL_ID_BYTES);
+        // NCCL carries only the plumbing here (handle exchange, scalar all-reduces, the graph broadcast; the
+        // C blocks move by copy engine): the NVLink-SHARP multicast set-up of ncclCommInitRank buys nothing and
+        // costs most of its 2 s at 8 ranks.  The caller's environment wins (GE_DIST_ROT=nccl users may want it).
+        setenv("NCCL_NVLS_ENABLE", "0", 0);
+        const auto tci = std::chrono::steady_clock::now();
         GE_NCCL(g_nccl.CommInitRank(&d->comm, world, id, rank));
+        if (getenv("GE_DEBUG"))
+            fprintf(stderr, "[dist init] ncclCommInitRank %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tci).count());
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
         GE_CUDA(cudaStreamCreateWithPriority(&d->cs, cudaStreamNonBlocking, hi));
