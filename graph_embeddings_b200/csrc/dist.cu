@@ -26,6 +26,7 @@
 // the round-1 plane (whole block, ncclSend/ncclRecv in the compute stream), GE_DIST_ROT=pipe the
 // half-block NCCL variant.
 #include "common.cuh"
+#include "shm_group.h"
 
 #include <dlfcn.h>
 
@@ -79,6 +80,8 @@ struct DistState {
     int nb = 0, m = 0;            // blocks per side, blocks per rank
     int32_t Bs = 0;               // ids per block
     int32_t row_base = 0, row_cnt = 0;  // first (virtual) id of the rank's rows; REAL rows it owns
+    ShmGroup* shm = nullptr;          // single-node host plumbing (shm_group.h); null = NCCL carries it
+    unsigned char id[GE_NCCL_ID_BYTES] = {};  // the job's unique id, kept for a late ncclCommInitRank
     int32_t layout = 0;               // 0 = contiguous blocks, 1 = cyclic (common.cuh ge_vid)
     int32_t lay_nb() const { return layout ? nb : 0; }
     int64_t nnz_global = 0;
@@ -131,6 +134,7 @@ void ge_dist_free(ge_ctx* ctx) {
     if (d->c0) cudaEventDestroy(d->c0);
     if (d->c1) cudaEventDestroy(d->c1);
     if (d->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(d->comm);
+    if (d->shm) { d->shm->close(); delete d->shm; }
     delete d;
     ctx->dist = nullptr;
 }
@@ -145,6 +149,59 @@ namespace {
             return GE_ERR_DIST;                                                          \
         }                                                                                \
     } while (0)
+
+// ---- host-level collectives of the ranks: shared memory on one node, else NCCL through a device word
+int ensure_comm(ge_ctx* ctx) {   // collective: every rank calls it at the same point
+    DistState* d = ctx->dist;
+    if (d->comm || d->world == 1) return GE_OK;
+    if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
+    NcclId id;
+    memcpy(&id, d->id, GE_NCCL_ID_BYTES);
+    const auto t0 = std::chrono::steady_clock::now();
+    GE_NCCL(g_nccl.CommInitRank(&d->comm, d->world, id, d->rank));
+    if (getenv("GE_DEBUG"))
+        fprintf(stderr, "[dist init] ncclCommInitRank %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    return GE_OK;
+}
+
+int plumb_allgather(ge_ctx* ctx, const void* mine, void* all, size_t n) {
+    DistState* d = ctx->dist;
+    if (d->world == 1) { memcpy(all, mine, n); return GE_OK; }
+    if (d->shm) return d->shm->allgather(mine, all, n, ctx->err) ? GE_OK : GE_ERR_DIST;
+    cudaStream_t st = ctx->stream;
+    unsigned char* dv = nullptr;
+    GE_CUDA(cudaMalloc(&dv, n * (size_t)(d->world + 1)));
+    cudaError_t e = cudaMemcpyAsync(dv + n * (size_t)d->world, mine, n, cudaMemcpyHostToDevice, st);
+    int nr = 0;
+    if (e == cudaSuccess) nr = g_nccl.AllGather(dv + n * (size_t)d->world, dv, n, NCCL_UINT8, d->comm, st);
+    if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(all, dv, n * (size_t)d->world, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
+    cudaFree(dv);
+    GE_CUDA(e);
+    GE_NCCL(nr);
+    return GE_OK;
+}
+
+// v[0..n) <- sum (op 0) or max (op 1) over the ranks, n <= 8
+int plumb_allreduce(ge_ctx* ctx, double* v, int n, int op) {
+    DistState* d = ctx->dist;
+    if (d->world == 1) return GE_OK;
+    double all[8 * 64];
+    if (n > 8 || d->world > 64) { ctx->err = "plumb_allreduce: too large"; return GE_ERR_INVALID; }
+    int r = plumb_allgather(ctx, v, all, sizeof(double) * (size_t)n);
+    if (r) return r;
+    for (int k = 0; k < n; k++) {
+        double a = all[k];
+        for (int q = 1; q < d->world; q++) { const double b = all[(size_t)q * n + k]; a = op ? (b > a ? b : a) : a + b; }
+        v[k] = a;   // every rank folds in rank order: identical bits everywhere
+    }
+    return GE_OK;
+}
+
+int plumb_barrier(ge_ctx* ctx) {
+    double z = 0;
+    return plumb_allreduce(ctx, &z, 1, 0);
+}
 
 __global__ void bucket_count(const int32_t* __restrict__ I, const int32_t* __restrict__ J, int64_t nnz,
                              int32_t row_base, int32_t Bs, int32_t nb, int32_t P, int32_t Hs,
@@ -301,17 +358,11 @@ int dist_map_peers(ge_ctx* ctx) {
     if (ok && cudaIpcGetMemHandle(&mine.ring, d->d_Cring) != cudaSuccess) { cudaGetLastError(); ok = false; }
     mine.ok = ok ? 1 : 0;
     // every rank takes part in the gather even when its own set-up failed
-    IpcPair* d_all = nullptr;
-    GE_CUDA(cudaMalloc(&d_all, sizeof(IpcPair) * (size_t)(d->world + 1)));
     std::vector<IpcPair> all(d->world);
-    cudaError_t e = cudaMemcpyAsync(d_all + d->world, &mine, sizeof(IpcPair), cudaMemcpyHostToDevice, st);
-    int nr = 0;
-    if (e == cudaSuccess) nr = g_nccl.AllGather(d_all + d->world, d_all, sizeof(IpcPair), NCCL_UINT8, d->comm, st);
-    if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(all.data(), d_all, sizeof(IpcPair) * (size_t)d->world, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
-    cudaFree(d_all);
-    GE_CUDA(e);
-    GE_NCCL(nr);
+    {
+        int r = plumb_allgather(ctx, &mine, all.data(), sizeof(IpcPair));
+        if (r) return r;
+    }
     for (int k = 0; k < d->world; k++) ok = ok && all[k].ok == 1;
     const int prev = (d->rank + d->world - 1) % d->world, next = (d->rank + 1) % d->world;
     if (ok) {
@@ -332,19 +383,14 @@ int dist_map_peers(ge_ctx* ctx) {
     }
     // agree on the plane: one rank that could not map its neighbour sends everybody to NCCL
     {
-        double* d_ok = nullptr;
-        GE_CUDA(cudaMalloc(&d_ok, 8));
         double hv = ok ? 0.0 : 1.0;
-        e = cudaMemcpyAsync(d_ok, &hv, 8, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) nr = g_nccl.AllReduce(d_ok, d_ok, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st);
-        if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(&hv, d_ok, 8, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
-        cudaFree(d_ok);
-        GE_CUDA(e);
-        GE_NCCL(nr);
+        int r = plumb_allreduce(ctx, &hv, 1, 0);
+        if (r) return r;
         if (hv != 0.0) {
             if (getenv("GE_DEBUG")) fprintf(stderr, "[graphemb] rank %d: CUDA IPC / stream memory operations unavailable, rotation falls back to NCCL send/recv\n", d->rank);
             d->rot = ROT_PIPE;
+            r = ensure_comm(ctx);   // every rank got the same sum: a collective call
+            if (r) return r;
         }
     }
     if (d->rot == ROT_CE && d->xfer_ev.empty()) {
@@ -375,17 +421,24 @@ extern "C" int ge_dist_init(ge_ctx* ctx, int32_t rank, int32_t world, const void
     ctx->dist = d;
     if (world > 1) {
         if (!id128) { ctx->err = "ge_dist_init: unique id required for world > 1"; return GE_ERR_INVALID; }
-        if (!g_nccl.load(ctx->err)) return GE_ERR_DIST;
-        NcclId id;
-        memcpy(&id, id128, GE_NCCL_ID_BYTES);
-        // NCCL carries only the plumbing here (handle exchange, scalar all-reduces, the graph broadcast; the
-        // C blocks move by copy engine): the NVLink-SHARP multicast set-up of ncclCommInitRank buys nothing and
-        // costs most of its 2 s at 8 ranks.  The caller's environment wins (GE_DIST_ROT=nccl users may want it).
-        setenv("NCCL_NVLS_ENABLE", "0", 0);
-        const auto tci = std::chrono::steady_clock::now();
-        GE_NCCL(g_nccl.CommInitRank(&d->comm, world, id, rank));
-        if (getenv("GE_DEBUG"))
-            fprintf(stderr, "[dist init] ncclCommInitRank %.1f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tci).count());
+        memcpy(d->id, id128, GE_NCCL_ID_BYTES);
+        // Plumbing.  With the copy-engine rotation NCCL would carry a few hundred bytes per epoch, and bringing it
+        // up costs 2.1 s (ncclCommInitRank, with or without NVLS) + 1.0 s (first collective) at 8 ranks: the ranks
+        // of one node meet in a shared-memory segment instead (shm_group.h) and NCCL is brought up only when a
+        // plane that moves data with it is selected (GE_DIST_ROT=nccl|pipe, IPC unavailable) or on request
+        // (GE_DIST_PLUMBING=nccl).
+        const char* rote = getenv("GE_DIST_ROT");
+        const char* plumb = getenv("GE_DIST_PLUMBING");
+        const bool want_nccl_data = (rote && (!strcmp(rote, "nccl") || !strcmp(rote, "pipe"))) || (!rote && getenv("GE_DIST_PIPE") && atoi(getenv("GE_DIST_PIPE")) == 1);
+        if (!(plumb && !strcmp(plumb, "nccl"))) {
+            d->shm = new ShmGroup();
+            std::string why;
+            if (!d->shm->open(id128, rank, world, why)) {   // fails on every rank or on none (the attach barrier)
+                if (getenv("GE_DEBUG")) fprintf(stderr, "[graphemb] rank %d: %s; plumbing falls back to NCCL\n", rank, why.c_str());
+                d->shm->close(); delete d->shm; d->shm = nullptr;
+            }
+        }
+        if (!d->shm || want_nccl_data) { int r = ensure_comm(ctx); if (r) return r; }
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
         GE_CUDA(cudaStreamCreateWithPriority(&d->cs, cudaStreamNonBlocking, hi));
@@ -483,22 +536,13 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
 
     GeLap lap(st, "dist prepare");
     // global max (f(x) weight uses it, GloveCost.java:19) and global nnz (cost normaliser)
-    double* d_tmp = nullptr;
-    GE_CUDA(cudaMalloc(&d_tmp, 16));
-    double h2[2] = {ctx->xmax, 0};
-    long long hn = ctx->nnz;
-    if (d->world > 1) {
-        GE_CUDA(cudaMemcpyAsync(d_tmp, &h2[0], 8, cudaMemcpyHostToDevice, st));
-        GE_NCCL(g_nccl.AllReduce(d_tmp, d_tmp, 1, NCCL_FLOAT64, NCCL_MAX, d->comm, st));
-        GE_CUDA(cudaMemcpyAsync(&h2[0], d_tmp, 8, cudaMemcpyDeviceToHost, st));
-        GE_CUDA(cudaMemcpyAsync(d_tmp + 1, &hn, 8, cudaMemcpyHostToDevice, st));
-        GE_NCCL(g_nccl.AllReduce(d_tmp + 1, d_tmp + 1, 1, NCCL_INT64, NCCL_SUM, d->comm, st));
-        GE_CUDA(cudaMemcpyAsync(&hn, d_tmp + 1, 8, cudaMemcpyDeviceToHost, st));
-        GE_CUDA(cudaStreamSynchronize(st));
-    }
-    cudaFree(d_tmp);
-    ctx->xmax = h2[0];
-    d->nnz_global = hn;
+    if (d->rot != ROT_CE) { r = ensure_comm(ctx); if (r) return r; }   // same environment on every rank: collective
+    double gmax = ctx->xmax, gnnz = (double)ctx->nnz;   // nnz < 2^53: exact in a double
+    r = plumb_allreduce(ctx, &gmax, 1, 1);
+    if (!r) r = plumb_allreduce(ctx, &gnnz, 1, 0);
+    if (r) return r;
+    ctx->xmax = gmax;
+    d->nnz_global = (long long)gnnz;
 
     // ---- K7: bucket the local nonzeros by (row-block, col-block)
     const int nbuckets = d->m * d->nb * d->P;
@@ -591,12 +635,9 @@ extern "C" int ge_dist_prepare(ge_ctx* ctx, int32_t nblocks) {
     if (d->world > 1 && d->peer_ring) {
         // re-prepare: nobody may free a ring a neighbour still has mapped -> unmap, then a barrier
         dist_unmap_peers(d);
-        double* d_b = nullptr;
-        GE_CUDA(cudaMalloc(&d_b, 8));
-        GE_CUDA(cudaMemsetAsync(d_b, 0, 8, st));
-        GE_NCCL(g_nccl.AllReduce(d_b, d_b, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st));
         GE_CUDA(cudaStreamSynchronize(st));
-        cudaFree(d_b);
+        r = plumb_barrier(ctx);
+        if (r) return r;
     }
     ge_free_store(ctx);
     ge_store_geometry(ctx);
@@ -738,9 +779,10 @@ extern "C" int ge_dist_train_epoch(ge_ctx* ctx, double* cost) {
     if (d->world == 1) d->head = (d->head + slots - (d->nb % slots)) % slots;  // nb shifts of an nb-ring: identity
     GE_CUDA(cudaEventRecord(ctx->ev1, st));
     double total = 0;
-    if (d->world > 1) GE_NCCL(g_nccl.AllReduce(ctx->d_cost, ctx->d_cost, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st));
+    if (d->world > 1 && !d->shm) GE_NCCL(g_nccl.AllReduce(ctx->d_cost, ctx->d_cost, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, st));
     GE_CUDA(cudaMemcpyAsync(&total, ctx->d_cost, sizeof(double), cudaMemcpyDeviceToHost, st));
     GE_CUDA(cudaStreamSynchronize(st));
+    if (d->world > 1 && d->shm) { int r = plumb_allreduce(ctx, &total, 1, 0); if (r) return r; }
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->update_seconds += ms * 1e-3;
@@ -829,15 +871,23 @@ extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const
                         (out_off[V] == 0 || (out_nbr && out_w)) && (in_off[V] == 0 || (in_nbr && in_w));
         hdr[0] = V; hdr[1] = ok ? out_off[V] : 0; hdr[2] = ok ? in_off[V] : 0; hdr[3] = ok;
     }
-    long long* d_hdr = nullptr;
-    GE_CUDA(cudaMalloc(&d_hdr, sizeof(hdr)));
-    cudaError_t e = cudaMemcpyAsync(d_hdr, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st);
-    int nr = e == cudaSuccess ? g_nccl.Broadcast(d_hdr, d_hdr, sizeof(hdr), NCCL_UINT8, root, d->comm, st) : 0;
-    if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(hdr, d_hdr, sizeof(hdr), cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
-    cudaFree(d_hdr);
-    GE_CUDA(e);
-    GE_NCCL(nr);
+    if (d->shm) {
+        long long allh[4 * 64];
+        if (d->world > 64) { ctx->err = "world too large"; return GE_ERR_INVALID; }
+        int rr = plumb_allgather(ctx, hdr, allh, sizeof(hdr));
+        if (rr) return rr;
+        memcpy(hdr, allh + 4 * (size_t)root, sizeof(hdr));
+    } else {
+        long long* d_hdr = nullptr;
+        GE_CUDA(cudaMalloc(&d_hdr, sizeof(hdr)));
+        cudaError_t e = cudaMemcpyAsync(d_hdr, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st);
+        int nr = e == cudaSuccess ? g_nccl.Broadcast(d_hdr, d_hdr, sizeof(hdr), NCCL_UINT8, root, d->comm, st) : 0;
+        if (e == cudaSuccess && !nr) e = cudaMemcpyAsync(hdr, d_hdr, sizeof(hdr), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess && !nr) e = cudaStreamSynchronize(st);
+        cudaFree(d_hdr);
+        GE_CUDA(e);
+        GE_NCCL(nr);
+    }
     if (!hdr[3]) { ctx->err = "bad graph arguments on the root rank"; return GE_ERR_INVALID; }
     lap.lap("header broadcast");
     int r = ge_graph_alloc(ctx, (int32_t)hdr[0], hdr[1], hdr[2]);
@@ -848,10 +898,47 @@ extern "C" int ge_dist_set_graph_csr(ge_ctx* ctx, int32_t root, int32_t V, const
         {ctx->d_out_off, out_off, ob}, {ctx->d_in_off, in_off, ob},
         {ctx->d_out_nbr, out_nbr, (size_t)ctx->E_out * 4}, {ctx->d_out_w, out_w, (size_t)ctx->E_out * 4},
         {ctx->d_in_nbr, in_nbr, (size_t)ctx->E_in * 4}, {ctx->d_in_w, in_w, (size_t)ctx->E_in * 4}};
-    for (const auto& q : parts) {
-        if (!q.n) continue;
-        if (me) { r = upload_staged(ctx, q.dv, q.h, q.n); if (r) { ge_free_graph(ctx); return r; } }
-        GE_NCCL(g_nccl.Broadcast(q.dv, q.dv, q.n, NCCL_UINT8, root, d->comm, st));
+    if (me)
+        for (const auto& q : parts)
+            if (q.n) { r = upload_staged(ctx, q.dv, q.h, q.n); if (r) { ge_free_graph(ctx); return r; } }
+    // peers pull the arrays out of the root's device memory (CUDA IPC, NVLink) when the node plumbing is up;
+    // else ncclBroadcast
+    bool via_ipc = d->shm != nullptr;
+    if (via_ipc) {
+        struct Handles { cudaIpcMemHandle_t h[6]; int32_t ok; int32_t pad[31]; };
+        Handles mine{};
+        std::vector<Handles> all(d->world);
+        if (me) {
+            mine.ok = 1;
+            GE_CUDA(cudaStreamSynchronize(st));   // uploads done before anybody reads
+            for (int k = 0; k < 6; k++)
+                if (parts[k].n && cudaIpcGetMemHandle(&mine.h[k], parts[k].dv) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
+        }
+        r = plumb_allgather(ctx, &mine, all.data(), sizeof(Handles));
+        if (r) return r;
+        void* src[6] = {};
+        double bad = all[root].ok ? 0.0 : 1.0;
+        if (!me && bad == 0.0)
+            for (int k = 0; k < 6; k++)
+                if (parts[k].n && cudaIpcOpenMemHandle(&src[k], all[root].h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); src[k] = nullptr; bad = 1.0; }
+        r = plumb_allreduce(ctx, &bad, 1, 0);
+        if (r) return r;
+        cudaError_t e = cudaSuccess;
+        if (bad == 0.0 && !me) {
+            for (int k = 0; k < 6 && e == cudaSuccess; k++)
+                if (parts[k].n) e = cudaMemcpyAsync(parts[k].dv, src[k], parts[k].n, cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+        for (int k = 0; k < 6; k++) if (src[k]) cudaIpcCloseMemHandle(src[k]);
+        GE_CUDA(e);
+        if (bad != 0.0) via_ipc = false;
+        else { r = plumb_barrier(ctx); if (r) return r; }   // the root's arrays stay untouched until every peer has its copy
+    }
+    if (!via_ipc) {
+        r = ensure_comm(ctx);
+        if (r) return r;
+        for (const auto& q : parts)
+            if (q.n) GE_NCCL(g_nccl.Broadcast(q.dv, q.dv, q.n, NCCL_UINT8, root, d->comm, st));
     }
     lap.lap("H2D on root + broadcasts");
     ctx->graph_seconds = 0;

@@ -982,7 +982,7 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 // 10-30 % off the single-thread loss in the first epoch, and moving such nonzeros into a launch of
 // their own changes the visiting order and with it the online loss (profiles/r02_hubs.md).  The
 // reference never has more writers on a row than threads.  So the launch itself is capped — the uniform
-// shuffled order is kept — to as many warps as put GE_HUB_SERIAL (default 8) on the hottest id.  Measured vs
+// shuffled order is kept — to as many warps as leave a bounded number of writers on the hottest id.  Measured vs
 // the single-thread oracle on that matrix, first epoch / later epochs: 16 on the hub 2.0 % / <= 0.6 %, 8 on
 // the hub 0.23 % / <= 0.13 %.  Inside the block schedule's buckets, where the hub is 12-50 % of a launch
 // instead of 5 %, the same count is less accurate (16: 38 %, 8: 2.0 % / <= 0.4 %), so the buckets use half
@@ -994,17 +994,30 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 // histograms) reaches GE_HUB_MASS (default 0.05).  The epoch then runs at the hub's own pace (count x
 // per-nonzero latency / writers), which is what bounded staleness on that row costs.  GE_HUB_SERIAL=0
 // switches the cap off.  Returns 0 = no cap.
+// How many writers: the measured error follows writers x share of the hottest id in the launch (single launch,
+// share 5.5 %: 16 writers 2 %, 8 writers 0.2 %; buckets, share 12-50 %: 8 writers 2 %, 4 writers 0.45 %), so
+// the cap allows GE_HUB_LOAD (0.5) / share writers, between 2 and GE_HOT_WRITERS — a mildly skewed launch (C3's
+// 8x8x2 buckets: hottest id 2.9 %) keeps 16 writers and a few hundred warps, a bucket that is half one column
+// runs nearly serially.  GE_HUB_SERIAL / GE_HUB_SERIAL_BLOCKS fix the number instead (sweeps).
 int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule) {
-    double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 8.0;
-    if (block_schedule) serial = getenv("GE_HUB_SERIAL_BLOCKS") ? atof(getenv("GE_HUB_SERIAL_BLOCKS")) : 0.5 * serial;
     const double theta = getenv("GE_HUB_MASS") ? atof(getenv("GE_HUB_MASS")) : 0.05;
     if (max_count <= 0 || launch_nnz <= 0) return 0;
     const double full = (double)ctx->sm_count * 32.0;
-    const double k = full * (double)max_count / (double)launch_nnz;   // warps of a full wave on the hottest id
+    const double share = (double)max_count / (double)launch_nnz;
+    const double k = full * share;   // warps of a full wave on the hottest id
     if (k > ctx->hub_kmax) ctx->hub_kmax = k;
     if (hub_mass > ctx->hub_mass_max) ctx->hub_mass_max = hub_mass;
+    double serial;
+    if (block_schedule && getenv("GE_HUB_SERIAL_BLOCKS")) serial = atof(getenv("GE_HUB_SERIAL_BLOCKS"));
+    else if (getenv("GE_HUB_SERIAL")) serial = atof(getenv("GE_HUB_SERIAL")) * (block_schedule ? 0.5 : 1.0);
+    else {
+        const double load = getenv("GE_HUB_LOAD") ? atof(getenv("GE_HUB_LOAD")) : 0.5;
+        const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
+        serial = load / share;
+        serial = serial < 2 ? 2 : (serial > writers ? writers : serial);
+    }
     if (serial <= 0 || hub_mass < theta || k <= serial) return 0;
-    const double w = serial * (double)launch_nnz / (double)max_count;
+    const double w = serial / share;
     ctx->capped_launches++;
     return w < 1 ? 1 : (int64_t)w;
 }

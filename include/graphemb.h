@@ -267,7 +267,10 @@ int ge_format_e(double v, char* out, int32_t cap);
 #define GE_NCCL_ID_BYTES 128
 /* rank 0 creates the id; the host distributes it (torch.distributed / file / env) */
 int ge_dist_unique_id(void* id128);
-/* world == 1 needs no id: the block schedule then runs on one GPU (rotation = pointer shift) */
+/* world == 1 needs no id: the block schedule then runs on one GPU (rotation = pointer shift).
+ * world > 1: the ranks of one node meet in a shared-memory segment named after the id (handles, scalars, barriers)
+ * and move data through CUDA IPC peer memory; an NCCL communicator is created only for GE_DIST_ROT=nccl|pipe,
+ * GE_DIST_PLUMBING=nccl, or when shared memory / IPC are unavailable. */
 int ge_dist_init(ge_ctx*, int32_t rank, int32_t world, const void* id128);
 /* this rank's id range in an nblocks x nblocks grid over V ids: build exactly these rows
  * (ge_cooc_build_rows) or import nonzeros whose rows lie in it */
