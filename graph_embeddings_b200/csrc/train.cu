@@ -994,11 +994,12 @@ int32_t ge_hot_count(ge_ctx* ctx, int64_t launch_nnz, int64_t span, int64_t warp
 // histograms) reaches GE_HUB_MASS (default 0.05).  The epoch then runs at the hub's own pace (count x
 // per-nonzero latency / writers), which is what bounded staleness on that row costs.  GE_HUB_SERIAL=0
 // switches the cap off.  Returns 0 = no cap.
-// How many writers: the measured error follows writers x share of the hottest id in the launch (single launch,
-// share 5.5 %: 16 writers 2 %, 8 writers 0.2 %; buckets, share 12-50 %: 8 writers 2 %, 4 writers 0.45 %), so
-// the cap allows GE_HUB_LOAD (0.5) / share writers, between 2 and GE_HOT_WRITERS — a mildly skewed launch (C3's
-// 8x8x2 buckets: hottest id 2.9 %) keeps 16 writers and a few hundred warps, a bucket that is half one column
-// runs nearly serially.  GE_HUB_SERIAL / GE_HUB_SERIAL_BLOCKS fix the number instead (sweeps).
+// How many writers: 8 in the single launch, 4 in a bucket of the block schedule (GE_HUB_SERIAL, GE_HUB_SERIAL_BLOCKS).
+// Scaling the number with the hottest id's share of the launch instead (GE_HUB_LOAD / share, between 2 and
+// GE_HOT_WRITERS; off unless GE_HUB_LOAD is set) was measured: fine for the single launch (9 writers, 0.38 %) but
+// 5.9 % in the first epoch of the block schedule, whose buckets hold several mid-sized hubs each.  The price of
+// the fixed 4: a mildly skewed matrix cut very finely (C3 in 8x8x2 buckets: hottest id 2.9 % of a bucket, damped
+// ids 12.7 %) runs its buckets on 137 warps.
 int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double hub_mass, bool block_schedule) {
     const double theta = getenv("GE_HUB_MASS") ? atof(getenv("GE_HUB_MASS")) : 0.05;
     if (max_count <= 0 || launch_nnz <= 0) return 0;
@@ -1007,13 +1008,11 @@ int64_t ge_warp_cap(ge_ctx* ctx, int64_t launch_nnz, int64_t max_count, double h
     const double k = full * share;   // warps of a full wave on the hottest id
     if (k > ctx->hub_kmax) ctx->hub_kmax = k;
     if (hub_mass > ctx->hub_mass_max) ctx->hub_mass_max = hub_mass;
-    double serial;
-    if (block_schedule && getenv("GE_HUB_SERIAL_BLOCKS")) serial = atof(getenv("GE_HUB_SERIAL_BLOCKS"));
-    else if (getenv("GE_HUB_SERIAL")) serial = atof(getenv("GE_HUB_SERIAL")) * (block_schedule ? 0.5 : 1.0);
-    else {
-        const double load = getenv("GE_HUB_LOAD") ? atof(getenv("GE_HUB_LOAD")) : 0.5;
+    double serial = getenv("GE_HUB_SERIAL") ? atof(getenv("GE_HUB_SERIAL")) : 8.0;
+    if (block_schedule) serial = getenv("GE_HUB_SERIAL_BLOCKS") ? atof(getenv("GE_HUB_SERIAL_BLOCKS")) : 0.5 * serial;
+    if (getenv("GE_HUB_LOAD")) {
         const double writers = getenv("GE_HOT_WRITERS") ? atof(getenv("GE_HOT_WRITERS")) : 16.0;
-        serial = load / share;
+        serial = atof(getenv("GE_HUB_LOAD")) / share;
         serial = serial < 2 ? 2 : (serial > writers ? writers : serial);
     }
     if (serial <= 0 || hub_mass < theta || k <= serial) return 0;
