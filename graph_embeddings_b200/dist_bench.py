@@ -65,7 +65,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
         h2d_direct = I.nbytes + J.nbytes + X.nbytes
         del I, J, X
     else:
-        nnz_local, _ = tr.build(g, root=0)     # ONE H2D on rank 0 + ncclBroadcast over NVLink
+        nnz_local, _ = tr.build(g, root=0)     # ONE H2D on rank 0, peers pull it over NVLink
     tp = mark("import" if direct else "handoff+build", tp)
     tr.prepare()
     tp = mark("prepare", tp)
@@ -161,7 +161,7 @@ def run(args, WORKLOADS, consts, log, peaks, ClockSampler, make_graph):
                 "e2e": {"value": nnz * K / float(A[:, 6].max()), "unit": "nnz_updates/s", "h2d_bytes_per_step": h2d / K,
                         "d2h_bytes_per_step": d2h * world / K, "seconds": float(A[:, 6].max()),
                         "phases_rank0": phases,
-                        "includes": ("host COO H2D import" if direct else "graph hand-off (one H2D on rank 0 + NCCL broadcast), sharded BCA build")
+                        "includes": ("host COO H2D import" if direct else "graph hand-off (one H2D on rank 0, peers pull it from its device memory over NVLink / CUDA IPC), sharded BCA build")
                                     + ", bucketing, store init, K epochs with loss all-reduce + read-back, "
                                     + ("f64 result (f32 over PCIe, widened on the host)" if extract_ok else "result D2H SKIPPED (host memory guard)")},
                 "gpu_launches": int(s1["launches"] - s0["launches"]) * world, "clocks": clk}
