@@ -111,3 +111,15 @@ def test_size_independent_properties_at_scale():
     r = oracle.cooc_build(g, first=12345, count=2000, threads=8)
     off = np.searchsorted(I, [12345, 14345])
     assert np.array_equal(J[off[0]:off[1]], r.J) and np.array_equal(X[off[0]:off[1]], r.X)
+
+
+@pytest.mark.parametrize("hubs", [1, 3])
+def test_odd_number_of_rows_in_the_global_tier(hubs):
+    """with an odd number of rows in the global-memory tier the launch rounds up to whole
+    blocks of two warps and the spare warp has no table.  Directed stars: each centre reaches its 300 leaves
+    (> 104 records: leaves the shared-memory tier), a leaf reaches only its centre — exactly `hubs` rows overflow."""
+    leaves = 300
+    edges = [(c * (leaves + 1), c * (leaves + 1) + 1 + k, 1.0) for c in range(hubs) for k in range(leaves)]
+    b, r = check(synth.tiny(edges, hubs * (leaves + 1)))
+    assert b.stats()["tier2_rows"] == hubs
+    assert np.diff(r.row_off).max() == leaves + 1
