@@ -100,6 +100,7 @@ SIGNATURES = {
     "ge_dist_set_graph_csr": (C.c_int, [_P, _I32, _I32, _P, _P, _P, _P, _P, _P]),
     "ge_dist_stats": (C.c_int, [_P, _P, _I32, C.POINTER(_F64), C.POINTER(_I64)]),
     "ge_dist_rotation_mode": (C.c_int, [_P]),
+    "ge_flatten_edges_static": (C.c_int, [_P, _I32, _I64, _I32, _P, _P, _P, _P, _P, _P, _P]),
 }
 
 

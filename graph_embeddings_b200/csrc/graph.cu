@@ -18,6 +18,7 @@
 // search.  All HBM-bound streaming; algorithmic bytes 12 B/edge in + 8 B/edge out per CSR.
 #include "common.cuh"
 
+#include <mutex>
 #include <utility>
 
 namespace {
@@ -354,5 +355,119 @@ extern "C" int ge_graph_export(ge_ctx* ctx, int64_t* out_off, int32_t* out_nbr, 
     if (in_nbr && ctx->E_in) GE_CUDA(cudaMemcpyAsync(in_nbr, ctx->d_in_nbr, (size_t)ctx->E_in * 4, cudaMemcpyDeviceToHost, st));
     if (in_w && ctx->E_in) GE_CUDA(cudaMemcpyAsync(in_w, ctx->d_in_w, (size_t)ctx->E_in * 4, cudaMemcpyDeviceToHost, st));
     GE_CUDA(cudaStreamSynchronize(st));
+    return GE_OK;
+}
+
+// ---- ge_flatten_edges_static: one direction of the flattening above with NO allocation ------------
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels as
+// build_direction; the sort buffers live in ONE file-scope device array that every GPU loading this
+// library holds until exit, inputs and outputs are the caller's device buffers, nothing is synchronised.
+// Every call shares the array: two calls that overlap on the GPU (different streams / handles) race.
+namespace {
+
+constexpr int64_t ST_MAX_E = GE_STATIC_MAX_EDGES;
+constexpr size_t ST_NB = (size_t)((ST_MAX_E + RS_TILE - 1) / RS_TILE);           // radix tiles at the maximum
+constexpr size_t ST_HIST_N = 256 * ST_NB;
+constexpr size_t ST_HIST_NB = (ST_HIST_N + RS_TILE - 1) / RS_TILE;
+constexpr size_t st_up(size_t b) { return (b + 255) & ~(size_t)255; }
+constexpr size_t ST_OFF_K0 = 0;
+constexpr size_t ST_OFF_K1 = ST_OFF_K0 + st_up((size_t)ST_MAX_E * 8);
+constexpr size_t ST_OFF_V0 = ST_OFF_K1 + st_up((size_t)ST_MAX_E * 8);
+constexpr size_t ST_OFF_V1 = ST_OFF_V0 + st_up((size_t)ST_MAX_E * 4);
+constexpr size_t ST_OFF_FLAG = ST_OFF_V1 + st_up((size_t)ST_MAX_E * 4);
+constexpr size_t ST_OFF_HIST = ST_OFF_FLAG + st_up((size_t)ST_MAX_E * 4);
+constexpr size_t ST_OFF_SUMS = ST_OFF_HIST + st_up(ST_HIST_N * 4);
+constexpr size_t ST_OFF_MISC = ST_OFF_SUMS + st_up(((ST_NB > ST_HIST_NB ? ST_NB : ST_HIST_NB) + 2) * 4 + 16);
+constexpr size_t ST_BYTES = ST_OFF_MISC + 256;  // misc: [0] bad-id flag, [1] number of unique keys
+
+static_assert(ST_BYTES == (size_t)GE_STATIC_SCRATCH_BYTES, "GE_STATIC_SCRATCH_BYTES in graphemb.h is stale");
+
+static __device__ __align__(256) unsigned char g_flatten_scratch[ST_BYTES];
+
+constexpr int ST_MAX_DEVICES = 64;
+unsigned char* g_flatten_base[ST_MAX_DEVICES] = {};  // DEVICE address of g_flatten_scratch, per device ordinal
+std::mutex g_flatten_setup;
+
+// offsets as offsets_by_search, the unique count read from the device; thread 0 publishes {count, bad flag}
+__global__ void offsets_by_search_static(const uint64_t* __restrict__ ukeys, const int32_t* __restrict__ misc, int32_t V,
+                                         int idbits, int64_t* __restrict__ off, int64_t* __restrict__ info) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t m = (int64_t)(uint32_t)misc[1];
+    if (v == 0) { info[0] = m; info[1] = misc[0]; }
+    if (v > V) return;
+    const uint64_t target = (uint64_t)v << idbits;
+    int64_t lo = 0, hi = m;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (ukeys[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    off[v] = lo;
+}
+
+}  // namespace
+
+extern "C" int ge_flatten_edges_static(ge_ctx* ctx, int32_t V, int64_t E, int32_t by_dst, const int32_t* d_src,
+                                       const int32_t* d_dst, const float* d_w, int64_t* d_off, int32_t* d_nbr,
+                                       float* d_wout, int64_t* d_info) {
+    if (!ctx) return GE_ERR_INVALID;
+    if (V <= 0 || E < 0 || !d_off || !d_info || (E > 0 && (!d_src || !d_dst || !d_w || !d_nbr || !d_wout))) {
+        ctx->err = "bad edge-list arguments";
+        return GE_ERR_INVALID;
+    }
+    if (E > ST_MAX_E) {
+        ctx->err = "ge_flatten_edges_static: E exceeds GE_STATIC_MAX_EDGES (" + std::to_string(ST_MAX_E) +
+                   " edges fit the static scratch); use ge_set_graph_edges";
+        return GE_ERR_INVALID;
+    }
+    const int dev = ctx->cfg.device;
+    if (dev < 0 || dev >= ST_MAX_DEVICES) { ctx->err = "device ordinal beyond the static scratch table"; return GE_ERR_INVALID; }
+    GE_CUDA(cudaSetDevice(dev));
+    {
+        std::lock_guard<std::mutex> lock(g_flatten_setup);
+        if (!g_flatten_base[dev]) {
+            // set-up, once per device, with that device current: in host code the array's name is only a
+            // stand-in for the symbol — the kernels need the address the runtime resolves for THIS device
+            void* p = nullptr;
+            GE_CUDA(cudaGetSymbolAddress((void**)&p, g_flatten_scratch));
+            if (!p) { ctx->err = "cudaGetSymbolAddress returned no address for the static scratch"; return GE_ERR_CUDA; }
+            g_flatten_base[dev] = (unsigned char*)p;
+        }
+    }
+    unsigned char* base = g_flatten_base[dev];
+    cudaStream_t st = ctx->stream;
+    int32_t* misc = (int32_t*)(base + ST_OFF_MISC);
+    if (E == 0) {  // also the warm-up call: resolves the address, touches no sort buffer
+        GE_CUDA(cudaMemsetAsync(d_off, 0, (size_t)(V + 1) * 8, st));
+        GE_CUDA(cudaMemsetAsync(d_info, 0, 16, st));
+        return GE_OK;
+    }
+    uint64_t *k0 = (uint64_t*)(base + ST_OFF_K0), *k1 = (uint64_t*)(base + ST_OFF_K1);
+    uint32_t *v0 = (uint32_t*)(base + ST_OFF_V0), *v1 = (uint32_t*)(base + ST_OFF_V1);
+    uint32_t *flag = (uint32_t*)(base + ST_OFF_FLAG), *hist = (uint32_t*)(base + ST_OFF_HIST), *sums = (uint32_t*)(base + ST_OFF_SUMS);
+    int idbits = 1;
+    while ((1LL << idbits) < V) idbits++;
+    const int nb = (int)((E + RS_TILE - 1) / RS_TILE);
+    const size_t hist_n = (size_t)256 * nb;
+    // the array keeps the last call's contents: the bad-id flag and the unique count must start at zero
+    // (keys, values, flags, histograms and tile sums are fully rewritten for the first E / nb entries)
+    GE_CUDA(cudaMemsetAsync(misc, 0, 256, st));
+    pack_keys<<<ctx->sm_count * 8, 256, 0, st>>>(d_src, d_dst, E, V, idbits, by_dst ? 1 : 0, k0, v0, misc);
+    for (int shift = 0; shift < 2 * idbits; shift += 8) {
+        rs_hist<<<nb, RS_THREADS, 0, st>>>(k0, E, shift, hist, nb);
+        int r = device_scan(ctx, hist, (int64_t)hist_n, hist, sums, nullptr);
+        if (r) return r;
+        rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, E, shift, hist, nb, k1, v1);
+        std::swap(k0, k1);
+        std::swap(v0, v1);
+    }
+    flag_heads<<<ctx->sm_count * 8, 256, 0, st>>>(k0, E, flag);
+    uint32_t* pos = v1;
+    int r = device_scan(ctx, flag, E, pos, sums, (uint32_t*)(misc + 1));
+    if (r) return r;
+    uint64_t* ukeys = k1;
+    compact_heads<<<ctx->sm_count * 8, 256, 0, st>>>(k0, v0, flag, pos, E, idbits, d_w, ukeys, d_nbr, d_wout);
+    offsets_by_search_static<<<(V + 1 + 255) / 256, 256, 0, st>>>(ukeys, misc, V, idbits, d_off, d_info);
+    GE_CUDA(cudaGetLastError());
     return GE_OK;
 }

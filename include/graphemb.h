@@ -308,6 +308,28 @@ int ge_dist_rotation_mode(ge_ctx*);
  * waiting for the peer) */
 int ge_dist_stats(ge_ctx*, int64_t* bucket_nnz, int32_t cap, double* comm_seconds, int64_t* nnz_global);
 
+/* --- allocation-free variant.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). ------------------------------------------------------------------------------- */
+#define GE_STATIC_MAX_EDGES 1048576        /* largest E the static scratch holds (2^20 edges)          */
+#define GE_STATIC_SCRATCH_BYTES 29623808   /* device memory every GPU that loads the library holds     */
+/* One direction of ge_set_graph_edges (by_dst = 0: out-lists, major id = src; 1: in-lists, major id = dst)
+ * computed by the same kernels, with the sort buffers in a file-scope device array instead of
+ * cudaMalloc'ed scratch.  Calls no cudaMalloc / cudaFree / allocating routine and does not synchronise:
+ * the work is queued on the handle's stream (ge_set_stream).  ALL data pointers are DEVICE memory
+ * of the handle's device, owned by the caller:
+ *   d_src, d_dst, d_w : E edges (vertex ids in [0, V), f32 weights)
+ *   d_off  [V + 1]    : list offsets
+ *   d_nbr, d_wout [E] : neighbours / weights, the first d_info[0] entries are written
+ *   d_info [2]        : {unique entries, 1 when a vertex id was out of range (outputs then meaningless)}
+ * E > GE_STATIC_MAX_EDGES -> GE_ERR_INVALID (use ge_set_graph_edges).  E == 0 writes zero offsets and is the
+ * warm-up call (resolves the scratch address for the device; call it once before a stream capture).
+ * Every call on a device shares the one scratch array: calls that overlap on the GPU (other streams,
+ * other handles, other threads) race — serialise them. */
+int ge_flatten_edges_static(ge_ctx*, int32_t V, int64_t E, int32_t by_dst, const int32_t* d_src,
+                            const int32_t* d_dst, const float* d_w, int64_t* d_off, int32_t* d_nbr,
+                            float* d_wout, int64_t* d_info);
+
 #ifdef __cplusplus
 }
 #endif
