@@ -1208,8 +1208,12 @@ struct ExtractStage {
 template <typename T>
 static cudaError_t extract_rows(ge_ctx* ctx, ExtractStage& S, const float* W, const float* C, int64_t rows, T* out) {
     const int32_t dim = ctx->cfg.dim;
+    // host threads of the drain: a handle that owns the machine (single-GPU trainer) uses up to 16, a rank of the
+    // block schedule shares the host with its peers and stays at 8; GE_HOST_THREADS overrides both
     unsigned nthr = std::thread::hardware_concurrency();
-    nthr = nthr < 1 ? 1 : (nthr > 8 ? 8 : nthr);
+    const unsigned cap = ctx->dist ? 8u : 16u;
+    nthr = nthr < 1 ? 1 : (nthr > cap ? cap : nthr);
+    if (const char* ev = getenv("GE_HOST_THREADS")) { const int v = atoi(ev); if (v >= 1 && v <= 64) nthr = (unsigned)v; }
     auto drain = [&](int64_t c) {  // chunk c: staging -> out
         const int64_t row0 = c * S.chunk_rows;
         const size_t n = (size_t)((rows - row0) < S.chunk_rows ? (rows - row0) : S.chunk_rows) * dim;
