@@ -3,6 +3,7 @@ include/graphemb.h declares; no compute call is made (there is no GPU here and n
 import ctypes as C
 import os
 import re
+import subprocess
 
 import pytest
 
@@ -88,3 +89,26 @@ def test_product_never_touches_the_oracle():
     _lib.build()
     needed = subprocess.run(["objdump", "-p", _lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "NEEDED" in needed and "oracle" not in needed
+
+
+def test_static_entry_point_allocates_nothing_and_resolves_its_scratch_address():
+    """ge_flatten_edges_static (no reference counterpart): its body must not call an allocator, must take the
+    device address of the static scratch with a checked cudaGetSymbolAddress, and the header's limits must
+    match the array that is compiled in."""
+    src = open(os.path.join(ROOT, "graph_embeddings_b200", "csrc", "graph.cu")).read()
+    body = src[src.index('extern "C" int ge_flatten_edges_static'):]
+    for banned in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "cudaMallocAsync", "new ", "malloc("):
+        assert banned not in body, banned
+    assert "GE_CUDA(cudaGetSymbolAddress((void**)&p, g_flatten_scratch))" in body
+    assert "static __device__ __align__(256) unsigned char g_flatten_scratch[ST_BYTES];" in src
+    hdr = open(os.path.join(ROOT, "include", "graphemb.h")).read()
+    max_e = int(re.search(r"#define GE_STATIC_MAX_EDGES (\d+)", hdr).group(1))
+    nbytes = int(re.search(r"#define GE_STATIC_SCRATCH_BYTES (\d+)", hdr).group(1))
+    up = lambda b: (b + 255) & ~255
+    nb = (max_e + 4095) // 4096
+    hist_nb = (256 * nb + 4095) // 4096
+    want = 2 * up(max_e * 8) + 3 * up(max_e * 4) + up(256 * nb * 4) + up((max(nb, hist_nb) + 2) * 4 + 16) + 256
+    assert nbytes == want and max_e == 1 << 20
+    _lib.build()
+    elf = subprocess.run(["cuobjdump", "-elf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "g_flatten_scratch" in elf                       # the array is in the device image of the library
